@@ -1,0 +1,171 @@
+/*
+ * ucnerf.h -- C ABI of libucnerf.so: the B200-native (sm_100a) UC-NeRF per-ray rendering hot path.
+ *
+ * This is the drop-in boundary.  The reference (wrld/UC-NeRF) has no FFI/plugin layer: its hot path is
+ * plain Python functions over torch tensors, so each entry point below names the reference function
+ * (file:line, relative to the reference repo) whose work it replaces; the Python mirror of those
+ * functions (uc-nerf_b200/*.py: same names, arguments, return tuples) binds them through ctypes.
+ * INTEGRATION.md shows the binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success, else a negative UCN_E_* code or a positive cudaError_t;
+ *     ucn_last_error() returns a human-readable string for the calling thread.
+ *   - all `const float*` / `float*` arguments are DEVICE pointers unless the name ends in `_host`.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); no call synchronises
+ *     except the *_host entry points, which copy H2D/D2H and synchronise `stream` before returning.
+ *   - kernels never allocate; callers own every buffer.  There is NO CPU fallback.
+ */
+#ifndef UCNERF_H
+#define UCNERF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UCN_MAX_V 8        /* source views                         */
+#define UCN_MAX_S 1024     /* samples per ray (multiple of 3)      */
+#define UCN_FEAT_C 8       /* channels of every feature map/volume */
+
+enum {
+  UCN_OK = 0,
+  UCN_E_ARG = -1,          /* bad argument (null pointer, S%3!=0, V>UCN_MAX_V, ...) */
+  UCN_E_UNSUPPORTED = -2,  /* device is not sm_100 or mode not compiled in          */
+  UCN_E_WORKSPACE = -3     /* workspace too small (see ucn_frame_workspace_bytes)   */
+};
+
+/* MLP arithmetic. FP32 = SIMT fp32 (parity mode, 1e-4 gate); BF16_TC = tcgen05 bf16, fp32 accumulate. */
+enum { UCN_MLP_FP32 = 0, UCN_MLP_BF16_TC = 1 };
+
+/* One target view ("frame"): cameras by value, packed maps by device pointer.
+ * Packed layouts (produced by ucn_pack_*):
+ *   nearfar[k] : [h_k][w_k][2]        first / last depth-hypothesis plane of stage k
+ *   vol[k]     : [D_k][h_k][w_k][8]   channels-last cost-feature volume of stage k
+ *   conf       : [H][W]               photometric confidence (as is)
+ *   rgb        : [V][H][W][4]         source images, rgb + zero pad
+ *   feat       : [V][H][W][8]         source FPN features, channels-last                        */
+typedef struct ucn_frame {
+  int32_t H, W, V, S;
+  int32_t D[3], h[3], w[3];
+  float K[9];               /* target intrinsics           (utils/utils.py:639-645)          */
+  float c2w[16];            /* target camera-to-world      (tgt_to_world)                    */
+  float w2c[16];            /* world-to-target             (world_to_ref)                    */
+  float near, far;          /* near_fars_ref[ref_idx]      (utils/utils.py:657,713-714)      */
+  float dir_rot0[9];        /* rotation of the view-dir feature for rays <  dir_switch       */
+  float dir_rot1[9];        /* ... and for rays >= dir_switch (reference quirk: renderer.py:241-243) */
+  int32_t dir_switch;
+  int32_t reserved;
+  float src_w2c[UCN_MAX_V * 16];
+  float src_K[UCN_MAX_V * 9];
+  const float *nearfar[3];
+  const float *vol[3];
+  const float *conf;
+  const float *rgb;
+  const float *feat;
+} ucn_frame;
+
+/* Packed UC-NeRF MLP weights (produced by ucn_pack_weights from the torch state_dict arrays). */
+typedef struct ucn_weights {
+  int32_t V;                /* source views the film/fb layers were built for */
+  int32_t reserved;
+  const float *f32;         /* fp32 pack: transposed [K][N] matrices + biases  */
+  const void *bf16;         /* bf16 pack: UMMA K-major core-matrix tiles (may be NULL if unused) */
+} ucn_weights;
+
+/* Pointers to the reference state_dict tensors (torch layout [out,in], fp32, DEVICE memory).
+ * network/models.py:87-104; the three layers forward() never touches are not needed. */
+typedef struct ucn_state_dict {
+  int32_t V, reserved;
+  const float *pts_w[6], *pts_b[6];      /* nerf.pts_linears.{0..5}                    */
+  const float *film_w, *film_b;          /* nerf.pts_bias_depth_fine    [128, 24+4V]   */
+  const float *fb_w, *fb_b;              /* nerf.pts_bias_confidence    [128, 8V]      */
+  const float *feature_w, *feature_b;    /* nerf.feature_linear         [128,128]      */
+  const float *views_w, *views_b;        /* nerf.views_linears.0        [64,155]       */
+  const float *vconf_w, *vconf_b;        /* nerf.view_confi_linears.0   [64,155]       */
+  const float *rgb_w, *rgb_b;            /* nerf.rgb_linear             [3,64]         */
+  const float *alpha_w, *alpha_b;        /* nerf.alpha_linear           [1,64]         */
+  const float *crgb_w, *crgb_b;          /* nerf.confi_rgb_linear       [3,128]        */
+  const float *alpha1_w, *alpha1_b;      /* nerf.alpha_linear_1         [1,128]        */
+} ucn_state_dict;
+
+/* ---- library ------------------------------------------------------------------------------- */
+int ucn_version(void);
+const char *ucn_last_error(void);
+/* number of kernel launches issued by this library since process start / last reset */
+int64_t ucn_launch_count(int reset);
+/* 0 if the current device is sm_100 (B200), else UCN_E_UNSUPPORTED */
+int ucn_check_device(void);
+
+/* ---- K0: packing (once per target view / per weight load) ----------------------------------- */
+/* src [B][C][N] -> dst [B][N][Cpad] (zero padded).  Replaces nothing in the reference: it is the
+ * relayout that lets the gathers below issue one 16/32-byte vector load per texel instead of C
+ * channel-strided 4-byte loads (NCDHW: utils/utils.py:869-890; NCHW: :776-788). */
+int ucn_pack_channels_last(const float *src, float *dst, int B, int Cn, int64_t N, int Cpad, void *stream);
+/* depth_values [D][h][w] -> [h][w][2] = (plane 0, plane D-1)   (utils/utils.py:668-683) */
+int ucn_pack_nearfar(const float *depth_values, float *dst, int D, int h, int w, void *stream);
+size_t ucn_weights_f32_bytes(int V);
+size_t ucn_weights_bf16_bytes(int V);
+int ucn_pack_weights(const ucn_state_dict *sd, float *dst_f32, void *dst_bf16, void *stream);
+
+/* ---- K1: ray generation + depth-bounded sampling (+ target-view NDC) -------------------------
+ * replaces get_rays_mvs (utils/utils.py:217-271, eval branch and explicit-pixel branch),
+ * sample_points_uniform (:393-397), build_rays_test (:600-739) and get_ndc_coordinate (:323-373).
+ * Rays are pixels ray0..ray0+R-1 of the row-major grid, or (pix_yx != NULL) explicit float
+ * (row, col) pairs laid out [2][R].  t_vals = linspace(0,1,S/3) (device).  t_rand [R][S] uniform
+ * jitter; if NULL an in-kernel Philox4x32-10 stream keyed by (seed, global ray, sample) is used.
+ * Outputs (any may be NULL except z): z [R][S], rays_d [R][3], pts [R][S][3], ndc [4][R][S][3]
+ * (stage1, stage2, stage3, ndc). */
+int ucn_raygen_sample(const ucn_frame *f, const float *pix_yx, int ray0, int R, const float *t_vals,
+                      const float *t_rand, uint64_t seed, float *z, float *rays_d, float *pts, float *ndc,
+                      void *stream);
+
+/* ---- K2: projection + fused gathers -> feature rows ----------------------------------------
+ * replaces index_point_feature (utils/utils.py:833-893), build_color_volume (:742-799),
+ * get_ndc_coordinate(sample_2d=True) (:323-347) and gen_pts_feats (network/renderer.py:177-212).
+ * feat [R*S][F], F = 24+12V+1, layout of input_feat (renderer.py:198-207).
+ * idx (optional) int32 [R*S][11+3V]: floor indices of every gather + in-bounds mask, for parity. */
+#define UCN_PART_VOLUMES 1   /* the three volume gathers + confidence (index_point_feature) */
+#define UCN_PART_VIEWS 2     /* per-source-view rgb/mask/feature gathers (build_color_volume) */
+#define UCN_PART_ALL 3
+/* `parts` selects which gathers run (others leave zeros), so the two reference functions can also be
+ * called on their own. */
+int ucn_gather(const ucn_frame *f, const float *pts, const float *ndc_s1, const float *ndc_s2,
+               const float *ndc_s3, int64_t n_samples, int parts, float *feat, int32_t *idx, void *stream);
+/* world points [n][3] -> [n][3] = (x/(W-1), y/(H-1), projective depth) for one camera:
+ * get_ndc_coordinate(..., sample_2d=True) (utils/utils.py:333-347,368-369). */
+int ucn_project_points(const float *w2c_host16, const float *K_host9, int H, int W, const float *pts, int64_t n,
+                       float *out, void *stream);
+/* same, positions recomputed from z (bit-identical to K1's): also emits ndc 'ndc' [R*S][3] */
+int ucn_gather_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R, float *feat,
+                      float *ndc_pts, void *stream);
+
+/* view-direction feature: gen_dir_feature + prologue of rendering (network/renderer.py:163-174,232-239) */
+int ucn_dir_feature(const ucn_frame *f, const float *rays_d, int R, int ray_offset, float *angle, void *stream);
+
+/* ---- K3: positional encoding + uncertainty-conditioned MLP ----------------------------------
+ * replaces Embedder.embed (network/models.py:50-54), run_network_mvs/batchify
+ * (network/renderer.py:57-106) and BaseAdapt_Renderer.forward (network/models.py:138-184).
+ * ndc_pts [N][3], feat [N][F], angle [R][3] (per ray; N = R*S) -> raw [N][4] = (rgb, sigma). */
+int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const float *feat, const float *angle, int R,
+                    int S, float *raw, int mode, void *stream);
+
+/* ---- K4: alpha compositing -------------------------------------------------------------------
+ * replaces raw2alpha / raw2outputs (network/renderer.py:25-36,109-140).  rgb [R][3], depth [R];
+ * acc/weights optional (acc [R], weights [R][S]); white_bkgd as in renderer.py:138-139. */
+int ucn_composite(const float *raw, const float *z, int R, int S, int white_bkgd, float *rgb, float *depth,
+                  float *acc, float *weights, void *stream);
+
+/* ---- whole frame --------------------------------------------------------------------------- */
+size_t ucn_frame_workspace_bytes(const ucn_frame *f, int R, int mode);
+/* K1 -> K2 -> K3 -> K4 for rays [ray0, ray0+R) on `stream`, everything device-resident.
+ * replaces the chunk loop of train.py:251-275.  out_rgb [R][3], out_depth [R]. */
+int ucn_render_rays(const ucn_frame *f, const ucn_weights *w, int ray0, int R, const float *t_vals,
+                    const float *t_rand, uint64_t seed, int mode, void *workspace, size_t workspace_bytes,
+                    float *out_rgb, float *out_depth, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UCNERF_H */

@@ -1,0 +1,299 @@
+"""GPU (-m gpu): the CUDA path, called through the reference-shaped Python API over the C-ABI, against
+(a) the CPU oracle on the same seeded inputs and (b) golden vectors produced by the reference's own code.
+
+Gates (BASELINE.json north_star / SURVEY.md §8d):
+  sample positions (z, pts, 4x ndc) and gather indices/masks ... bit-exact
+  feature rows ............................................... <= 1e-5 abs
+  fp32 path rgb / depth ...................................... <= 1e-4 abs
+  bf16 tcgen05 path .......................................... <= 1e-3 abs per-pixel rgb, <= 0.05 dB PSNR
+"""
+import copy
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import CASES, bits, load_case
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def T(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def ref_inputs(c):
+    """The dicts/tensors the reference's eval loop passes around (train.py:238-272), on the GPU."""
+    sc = c["scene"]
+    outputs = {f"stage{k + 1}": {"depth_values": T(sc.depth_values[k]), "volume_feature_no_ref": T(sc.volumes[k])}
+               for k in range(3)}
+    outputs["stage3"]["img_feats"] = T(sc.img_feats)
+    pose_ref = {"w2cs": T(sc.w2cs), "intrinsics": T(sc.K), "c2ws": T(sc.c2ws), "near_fars": T(sc.near_fars)}
+    return outputs, pose_ref, T(sc.imgs), T(sc.confidence)
+
+
+def make_model(c, mode):
+    from ucnerf_b200 import models
+    m = models.UCNeRF(D=6, W=128, input_ch_pts=63, skips=[4], input_ch_views=27, input_ch_feat=c["scene"].feat_dim,
+                      view_num=c["V"] + 1, mode=mode)
+    m.load_state_dict({k: torch.from_numpy(v) for k, v in c["weights"].items()})
+    return m.to(DEV)
+
+
+def make_query(mode="fp32"):
+    from ucnerf_b200 import models, renderer
+    embed_fn, _ = models.get_embedder(10, 0)
+    embeddirs_fn, _ = models.get_embedder(4, 0)
+    return lambda pts, dirs, feats, fn: renderer.run_network_mvs(pts, dirs, feats, fn, embed_fn=embed_fn,
+                                                                 embeddirs_fn=embeddirs_fn, netchunk=1024)
+
+
+def psnr(a, b):
+    return -10.0 * np.log10(np.mean((a - b) ** 2) + 1e-20)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_build_rays_test_bit_exact(name):
+    from ucnerf_b200 import rays
+    c = load_case(name)
+    g, sc = c["g"], c["scene"]
+    outputs, pose_ref, _, _ = ref_inputs(c)
+    H, W, S, chunk = c["H"], c["W"], c["S"], c["chunk"]
+    osc = O.OracleScene(sc, S)
+    n_chunks = (H * W + chunk - 1) // chunk
+    for idx in range(n_chunks):
+        lo, hi = idx * chunk, min(H * W, (idx + 1) * chunk)
+        pts, dirs, ndc, z, rays_o, ndcp = rays.build_rays_test(
+            H, W, pose_ref["c2ws"][0], pose_ref["w2cs"][0], pose_ref["intrinsics"][0], pose_ref["near_fars"],
+            pose_ref["near_fars"][-1], S, chunk=chunk, idx=idx, outputs=outputs, t_rand=T(c["t_rand"][lo:hi]))
+        py, px = O.chunk_pixels(H, W, chunk, idx)
+        o = O.build_rays_test(osc, py, px, c["t_rand"][lo:hi])
+        for got, want_o, want_g in ((z, o["z"], g["z"][lo:hi]), (pts, o["pts"], g["pts"][lo:hi]),
+                                    (dirs, o["rays_d"], g["rays_d"][lo:hi])):
+            got = got.cpu().numpy()
+            assert np.array_equal(bits(got), bits(want_o))
+            assert np.array_equal(bits(got), bits(want_g))
+        for k in ("stage1", "stage2", "stage3", "ndc"):
+            got = ndc[k].cpu().numpy()
+            assert np.array_equal(bits(got), bits(o["ndc"][k])), k
+            assert np.array_equal(bits(got), bits(g[k][lo:hi])), k
+        assert rays_o.shape == (hi - lo, 3) and torch.equal(rays_o[0], pose_ref["c2ws"][0][:3, 3])
+        assert set(ndcp) == {"w2c_ref", "intrinsic_ref", "inv_scale", "near", "far", "pad"}
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_gather_indices_and_features(name):
+    from ucnerf_b200 import rays, renderer
+    c = load_case(name)
+    g, sc = c["g"], c["scene"]
+    outputs, pose_ref, imgs, conf = ref_inputs(c)
+    pose_src = {"w2cs": pose_ref["w2cs"][1:], "intrinsics": pose_ref["intrinsics"][1:]}
+    osc = O.OracleScene(sc, c["S"])
+    ndc = {k: T(g[k]) for k in ("stage1", "stage2", "stage3", "ndc")}
+    pts = T(g["pts"])
+    feat, idx = rays.gather_features(outputs, imgs, outputs["stage3"]["img_feats"], conf, pose_src, pts, ndc, with_idx=True)
+    ndc_all = np.stack([g[k] for k in ("stage1", "stage2", "stage3", "ndc")])
+    feat_o, idx_o = O.gen_pts_feats(osc, g["pts"], ndc_all, with_idx=True)
+    assert np.array_equal(idx.cpu().numpy(), idx_o)                       # floor indices + masks: bit-exact
+    feat = feat.cpu().numpy()
+    assert np.abs(feat - feat_o).max() <= 1e-5
+    assert np.abs(feat[::c["stride"]] - g["feat_sub"]).max() <= 1e-5      # vs the reference's gen_pts_feats
+    # the two reference functions on their own
+    vf, cs = rays.index_point_feature(outputs, conf.reshape(1, 1, 1, c["H"], c["W"]), ndc)
+    assert np.array_equal(vf.cpu().numpy(), feat[..., :24]) and np.array_equal(cs.cpu().numpy(), feat[..., -1])
+    cv = rays.build_color_volume(pts, pose_src, imgs, img_feat=outputs["stage3"]["img_feats"], with_mask=True)
+    assert np.array_equal(cv.cpu().numpy(), feat[..., 24:-1])
+    f2 = renderer.gen_pts_feats(imgs, outputs, pts, pose_src, ndc, sc.feat_dim, outputs["stage3"]["img_feats"],
+                                confidence=conf)
+    assert np.array_equal(f2.cpu().numpy(), feat)
+
+
+def test_gather_matches_torch_grid_sample():
+    """Cross-check against the library op the reference calls (F.grid_sample on this GPU)."""
+    import torch.nn.functional as F
+    from ucnerf_b200 import rays
+    c = load_case("small_v3")
+    g = c["g"]
+    outputs, pose_ref, imgs, conf = ref_inputs(c)
+    ndc = {k: T(g[k]) for k in ("stage1", "stage2", "stage3", "ndc")}
+    vf, cs = rays.index_point_feature(outputs, conf.reshape(1, 1, 1, c["H"], c["W"]), ndc)
+    R, S = g["z"].shape
+    for k, name in enumerate(("stage1", "stage2", "stage3")):
+        grid = ndc[name].view(-1, 1, R, S, 3) * 2 - 1.0
+        want = F.grid_sample(outputs[name]["volume_feature_no_ref"], grid, align_corners=False, mode="bilinear",
+                             padding_mode="border")[:, :, 0].permute(2, 3, 0, 1).squeeze()
+        assert (vf[..., 8 * k:8 * k + 8] - want).abs().max().item() <= 1e-5
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_mlp_fp32_and_composite(name):
+    from ucnerf_b200 import renderer
+    c = load_case(name)
+    g = c["g"]
+    model = make_model(c, "fp32")
+    ow = O.OracleWeights(c["weights"], c["V"])
+    R, S = g["z"].shape
+    feat_o = O.gen_pts_feats(O.OracleScene(c["scene"], S), g["pts"],
+                             np.stack([g[k] for k in ("stage1", "stage2", "stage3", "ndc")]))
+    raw = make_query()(T(g["ndc"]), T(g["angle"]), T(feat_o), model).cpu().numpy()
+    raw_o = O.run_network(ow, g["ndc"], feat_o, g["angle"])
+    assert np.abs(raw - raw_o).max() <= 1e-4
+    assert np.abs(raw - g["raw"]).max() <= 1e-4
+    # UCNeRF.forward on the reference's concatenated [PE | feat | PE] input
+    from ucnerf_b200 import models
+    e0, _ = models.get_embedder(10, 0)
+    e1, _ = models.get_embedder(4, 0)
+    sub = slice(0, 40)
+    x = torch.cat([e0(T(g["ndc"][sub])), T(feat_o[sub]), e1(T(g["angle"][sub])[:, None].expand(-1, S, -1))], -1)
+    assert (model(x).cpu().numpy() - g["raw"][sub]).max() <= 1e-4
+    rgb, disp, acc, w, depth, w2, var = renderer.raw2outputs(T(g["raw"]), T(g["z"]), None)
+    assert np.abs(rgb.cpu().numpy() - g["rgb"]).max() <= 1e-4
+    assert np.abs(depth.cpu().numpy() - g["depth"]).max() <= 1e-4
+    rgb_o, depth_o = O.raw2outputs(g["raw"], g["z"])
+    assert np.abs(rgb.cpu().numpy() - rgb_o).max() <= 1e-5
+    assert np.abs(acc.cpu().numpy() - w.sum(1).cpu().numpy()).max() <= 1e-5
+
+
+def _reference_loop(c, mode):
+    """The reference's eval loop verbatim (train.py:251-275) on the drop-in API."""
+    from ucnerf_b200 import rays, renderer
+    outputs, pose_ref, imgs, conf = ref_inputs(c)
+    H, W, S, chunk, V = c["H"], c["W"], c["S"], c["chunk"], c["V"]
+    args = SimpleNamespace(view_num=V + 1, feat_dim=c["scene"].feat_dim, img_downscale=1.0, use_color_volume=False,
+                           net_type="v0", netchunk=1024)
+    model, query = make_model(c, mode), make_query()
+    near_fars = pose_ref["near_fars"]
+    tgt_to_world, world_to_ref, intrinsic = pose_ref["c2ws"][0], pose_ref["w2cs"][0], pose_ref["intrinsics"][0]
+    rgbs, depths = [], []
+    for idx in range((H * W + chunk - 1) // chunk):
+        lo, hi = idx * chunk, min(H * W, (idx + 1) * chunk)
+        pts, dirs, ndc, z, rays_o, ndcp = rays.build_rays_test(H, W, tgt_to_world, world_to_ref, intrinsic, near_fars,
+                                                               near_fars[-1], S, chunk=chunk, idx=idx, outputs=outputs,
+                                                               t_rand=T(c["t_rand"][lo:hi]))
+        rgb, depth = renderer.rendering(args, pose_ref, pts, ndc, z, dirs, outputs, imgs, near_fars=near_fars[0],
+                                        img_feat=outputs["stage3"]["img_feats"], confidence=conf, ndc_parameters=ndcp,
+                                        network_fn=model, network_query_fn=query)
+        rgbs.append(rgb.cpu())
+        depths.append(depth.cpu())
+    assert pose_ref["w2cs"].shape[0] == V                     # stripped in place, like the reference (Q4)
+    return torch.cat(rgbs).numpy(), torch.cat(depths).numpy()
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_drop_in_eval_loop_fp32(name):
+    c = load_case(name)
+    rgb, depth = _reference_loop(c, "fp32")
+    assert np.abs(rgb - c["g"]["rgb"]).max() <= 1e-4
+    assert np.abs(depth - c["g"]["depth"]).max() <= 1e-4
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_whole_frame_fp32(name):
+    from ucnerf_b200.frame import FrameRenderer, PackedFrame, PackedWeights
+    c = load_case(name)
+    fr = PackedFrame.from_scene(c["scene"], c["S"], DEV, dir_switch=c["chunk"])
+    pw = PackedWeights(c["weights"], c["V"], DEV)
+    rgb, depth = FrameRenderer(fr, pw, "fp32").render(t_rand=T(c["t_rand"]))
+    assert np.abs(rgb.cpu().numpy() - c["g"]["rgb"]).max() <= 1e-4
+    assert np.abs(depth.cpu().numpy() - c["g"]["depth"]).max() <= 1e-4
+    # ragged: sub-range of rays with a small workspace == the same rays of the full render, bit-identical
+    n = c["H"] * c["W"]
+    r2, d2 = FrameRenderer(fr, pw, "fp32", max_rays=97).render(ray0=33, n_rays=n - 70, t_rand=T(c["t_rand"][33:n - 37]))
+    assert torch.equal(r2, rgb[33:n - 37]) and torch.equal(d2, depth[33:n - 37])
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_whole_frame_bf16_tensor_core(name):
+    from ucnerf_b200.frame import FrameRenderer, PackedFrame, PackedWeights
+    c = load_case(name)
+    g = c["g"]
+    fr = PackedFrame.from_scene(c["scene"], c["S"], DEV, dir_switch=c["chunk"])
+    pw = PackedWeights(c["weights"], c["V"], DEV)
+    rgb, depth = FrameRenderer(fr, pw, "bf16").render(t_rand=T(c["t_rand"]))
+    rgb = rgb.cpu().numpy()
+    assert np.abs(rgb - g["rgb"]).max() <= 1e-3
+    pseudo_gt = np.random.default_rng(5).random(g["rgb"].shape).astype(np.float32)
+    assert abs(psnr(rgb, pseudo_gt) - psnr(g["rgb"], pseudo_gt)) <= 0.05
+
+
+def test_edge_cases():
+    """Empty ray sets, out-of-frustum samples (mask 0, border clamp), explicit-pixel ray lists."""
+    from ucnerf_b200 import rays
+    from ucnerf_b200.frame import FrameRenderer, PackedFrame, PackedWeights
+    c = load_case("small_v3")
+    sc = copy.deepcopy(c["scene"])
+    sc.w2cs[1, 0, 3] += 3.0                       # push source view 1 far sideways: most samples project outside
+    sc.c2ws[1] = np.linalg.inv(sc.w2cs[1])
+    S = c["S"]
+    osc = O.OracleScene(sc, S)
+    py, px = O.chunk_pixels(c["H"], c["W"])
+    o = O.build_rays_test(osc, py, px, c["t_rand"])
+    feat_o, idx_o = O.gen_pts_feats(osc, o["pts"], o["ndc_all"], with_idx=True)
+    assert (idx_o[..., 13] == 0).mean() > 0.5     # the shifted view really is mostly masked out
+    fr = PackedFrame.from_scene(sc, S, DEV)
+    outputs = {f"stage{k + 1}": {"volume_feature_no_ref": T(sc.volumes[k])} for k in range(3)}
+    pose_src = {"w2cs": T(sc.w2cs[1:]), "intrinsics": T(sc.K[1:])}
+    feat, idx = rays.gather_features(outputs, T(sc.imgs), T(sc.img_feats), T(sc.confidence), pose_src, T(o["pts"]),
+                                     {k: T(v) for k, v in o["ndc"].items()}, with_idx=True)
+    assert np.array_equal(idx.cpu().numpy(), idx_o)
+    assert np.abs(feat.cpu().numpy() - feat_o).max() <= 1e-5
+    pw = PackedWeights(c["weights"], c["V"], DEV)
+    rgb, depth = FrameRenderer(fr, pw, "fp32").render(ray0=5, n_rays=0)
+    assert rgb.shape == (0, 3) and depth.shape == (0,)
+    # explicit pixel list == the same pixels of the grid
+    ys, xs = T(py[40:90]), T(px[40:90])
+    _, d, pix = rays.get_rays_for_pixels(c["H"], c["W"], T(sc.K[0]), T(sc.c2ws[0]), ys, xs)
+    assert np.array_equal(bits(d.cpu().numpy()), bits(o["rays_d"][40:90]))
+
+
+def test_philox_jitter_statistics_and_sortedness():
+    """No t_rand given: in-kernel Philox jitter.  z stays inside its stratum, so z is sorted per ray;
+    a different seed changes the draw; the same seed reproduces it bit-for-bit."""
+    from ucnerf_b200 import rays
+    c = load_case("s126_v3")
+    outputs, pose_ref, _, _ = ref_inputs(c)
+    a = (c["H"], c["W"], pose_ref["c2ws"][0], pose_ref["w2cs"][0], pose_ref["intrinsics"][0], pose_ref["near_fars"],
+         pose_ref["near_fars"][-1], c["S"])
+    z1 = rays.build_rays_test(*a, outputs=outputs, seed=1)[3]
+    z1b = rays.build_rays_test(*a, outputs=outputs, seed=1)[3]
+    z2 = rays.build_rays_test(*a, outputs=outputs, seed=2)[3]
+    assert torch.equal(z1, z1b) and not torch.equal(z1, z2)
+    assert bool((z1[:, 1:] >= z1[:, :-1]).all())
+    # jitter uniformity: reconstruct u from the un-jittered strata
+    z0 = rays.build_rays_test(*a, outputs=outputs, t_rand=torch.zeros_like(z1))[3]
+    zh = rays.build_rays_test(*a, outputs=outputs, t_rand=torch.ones_like(z1))[3]
+    u = ((z1 - z0) / (zh - z0).clamp_min(1e-12))[(zh - z0) > 1e-6]
+    assert 0.45 < u.mean().item() < 0.55 and 0.0 <= u.min().item() and u.max().item() <= 1.0 + 1e-4
+
+
+def test_config1_size_properties():
+    """BASELINE config-1 shapes (320x256, 3 views, 126 samples): oracle on a ray subset + size-independent
+    properties (row-tile sharding bit-identical to the whole frame)."""
+    from ucnerf_b200 import synthetic
+    from ucnerf_b200.frame import FrameRenderer, PackedFrame, PackedWeights
+    H, W, V, S = 256, 320, 3, 126
+    sc = synthetic.make_scene(H, W, V, seed=11)
+    wts = synthetic.make_weights(V, seed=11)
+    fr = PackedFrame.from_scene(sc, S, DEV, dir_switch=1024)
+    pw = PackedWeights(wts, V, DEV)
+    t_rand = torch.rand((H * W, S), device=DEV, generator=torch.Generator(DEV).manual_seed(3))
+    for mode, tol in (("fp32", 1e-4), ("bf16", 1e-3)):
+        ren = FrameRenderer(fr, pw, mode, max_rays=H * W // 2)
+        rgb, depth = ren.render(t_rand=t_rand)
+        # sharded into 8 row tiles == whole frame, bit-identical
+        from ucnerf_b200 import shard
+        tiles = [ren.render(*shard.row_tile(H, W, p, 8), t_rand=t_rand[slice(*np.cumsum(shard.row_tile(H, W, p, 8)))])
+                 for p in range(8)]
+        assert torch.equal(torch.cat([t[0] for t in tiles]), rgb)
+        # oracle on three 256-ray windows (incl. the dir-frame switch at ray 1024)
+        osc, ow = O.OracleScene(sc, S, dir_switch=1024), O.OracleWeights(wts, V)
+        tr = t_rand.cpu().numpy()
+        for ray0 in (0, 900, H * W - 256):
+            rgb_o, depth_o = O.render_rays(osc, ow, ray0, 256, tr[ray0:ray0 + 256])
+            assert np.abs(rgb[ray0:ray0 + 256].cpu().numpy() - rgb_o).max() <= tol, mode
+            if mode == "fp32":
+                assert np.abs(depth[ray0:ray0 + 256].cpu().numpy() - depth_o).max() <= 1e-4

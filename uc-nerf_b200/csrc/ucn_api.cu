@@ -1,0 +1,99 @@
+// ucn_api.cu -- library plumbing (errors, launch accounting, device check), MLP mode dispatch and the
+// whole-frame chain K1 -> K2 -> K3 -> K4 that replaces the reference's per-chunk Python loop
+// (train.py:251-275).
+#include <stdio.h>
+#include <string.h>
+
+#include <atomic>
+
+#include "ucn_common.cuh"
+
+static thread_local char g_err[512] = "";
+static std::atomic<int64_t> g_launches{0};
+
+int ucn_set_error(int code, const char *msg) {
+  snprintf(g_err, sizeof(g_err), "%s", msg);
+  return code;
+}
+int ucn_cuda_status(cudaError_t e, const char *where) {
+  snprintf(g_err, sizeof(g_err), "%s: %s (%s)", where, cudaGetErrorString(e), cudaGetErrorName(e));
+  return (int)e;
+}
+void ucn_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int ucn_mlp_forward_fp32(const ucn_weights *w, const float *ndc_pts, const float *feat, const float *angle, int R,
+                         int S, float *raw, void *stream);
+int ucn_mlp_forward_tc(const ucn_weights *w, const float *ndc_pts, const float *feat, const float *angle, int R,
+                       int S, float *raw, void *stream);
+
+extern "C" int ucn_version(void) { return 100; }
+extern "C" const char *ucn_last_error(void) { return g_err; }
+extern "C" int64_t ucn_launch_count(int reset) {
+  return reset ? g_launches.exchange(0) : g_launches.load();
+}
+
+extern "C" int ucn_check_device(void) {
+  int dev = 0, major = 0, minor = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return ucn_cuda_status(e, "cudaGetDevice");
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
+  if (major != 10) {
+    snprintf(g_err, sizeof(g_err), "libucnerf is built for sm_100a only; device %d is sm_%d%d", dev, major, minor);
+    return UCN_E_UNSUPPORTED;
+  }
+  return UCN_OK;
+}
+
+extern "C" int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const float *feat, const float *angle,
+                               int R, int S, float *raw, int mode, void *stream) {
+  UCN_CHECK_ARG(w && ndc_pts && feat && angle && raw, "ucn_mlp_forward: null argument");
+  UCN_CHECK_ARG(w->V >= 1 && w->V <= UCN_MAX_V, "ucn_mlp_forward: 1 <= V <= 8");
+  UCN_CHECK_ARG(S > 0, "ucn_mlp_forward: S <= 0");
+  if (R <= 0) return UCN_OK;
+  if (mode == UCN_MLP_FP32) return ucn_mlp_forward_fp32(w, ndc_pts, feat, angle, R, S, raw, stream);
+  if (mode == UCN_MLP_BF16_TC) return ucn_mlp_forward_tc(w, ndc_pts, feat, angle, R, S, raw, stream);
+  return ucn_set_error(UCN_E_ARG, "ucn_mlp_forward: unknown mode");
+}
+
+// workspace carve-up for ucn_render_rays (all 256-byte aligned)
+namespace {
+struct Workspace {
+  size_t z, rays_d, angle, ndc, feat, raw, total;
+  Workspace(const ucn_frame *f, int R) {
+    const size_t N = (size_t)R * f->S, F = 24 + 12 * (size_t)f->V + 1;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 255) & ~size_t(255); return r; };
+    z = take(N * 4); rays_d = take((size_t)R * 12); angle = take((size_t)R * 12);
+    ndc = take(N * 12); feat = take(N * F * 4); raw = take(N * 16);
+    total = o;
+  }
+};
+}  // namespace
+
+extern "C" size_t ucn_frame_workspace_bytes(const ucn_frame *f, int R, int mode) {
+  (void)mode;
+  if (!f || R <= 0) return 0;
+  return Workspace(f, R).total;
+}
+
+extern "C" int ucn_render_rays(const ucn_frame *f, const ucn_weights *w, int ray0, int R, const float *t_vals,
+                               const float *t_rand, uint64_t seed, int mode, void *workspace, size_t workspace_bytes,
+                               float *out_rgb, float *out_depth, void *stream) {
+  UCN_CHECK_ARG(f && w && t_vals && workspace && out_rgb && out_depth, "ucn_render_rays: null argument");
+  UCN_CHECK_ARG(w->V == f->V, "ucn_render_rays: weights were packed for a different number of source views");
+  if (R <= 0) return UCN_OK;
+  const Workspace ws(f, R);
+  if (workspace_bytes < ws.total) return ucn_set_error(UCN_E_WORKSPACE, "ucn_render_rays: workspace too small");
+  char *base = reinterpret_cast<char *>(workspace);
+  float *z = reinterpret_cast<float *>(base + ws.z), *rays_d = reinterpret_cast<float *>(base + ws.rays_d);
+  float *angle = reinterpret_cast<float *>(base + ws.angle), *ndc = reinterpret_cast<float *>(base + ws.ndc);
+  float *feat = reinterpret_cast<float *>(base + ws.feat), *raw = reinterpret_cast<float *>(base + ws.raw);
+  int rc;
+  if ((rc = ucn_raygen_sample(f, nullptr, ray0, R, t_vals, t_rand, seed, z, rays_d, nullptr, nullptr, stream))) return rc;
+  if ((rc = ucn_dir_feature(f, rays_d, R, ray0, angle, stream))) return rc;
+  if ((rc = ucn_gather_from_z(f, z, nullptr, ray0, R, feat, ndc, stream))) return rc;
+  if ((rc = ucn_mlp_forward(w, ndc, feat, angle, R, f->S, raw, mode, stream))) return rc;
+  if ((rc = ucn_composite(raw, z, R, f->S, 0, out_rgb, out_depth, nullptr, nullptr, stream))) return rc;
+  return UCN_OK;
+}

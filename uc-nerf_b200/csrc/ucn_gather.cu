@@ -1,0 +1,214 @@
+// ucn_gather.cu -- K2: per-sample projection into the source views + fused bilinear/trilinear gathers,
+// assembled into the reference's input_feat row layout.
+//
+// replaces (reference): utils/utils.py:833-893 index_point_feature, :742-799 build_color_volume,
+//   :323-347 get_ndc_coordinate(sample_2d=True); network/renderer.py:177-212 gen_pts_feats.
+//
+// Data layout (see ucn_pack.cu): all maps are channels-last so one texel is one 16/32-byte vector load
+// (volume/feature texel = 8 fp32 = one 32 B sector; rgb texel = float4).  One thread owns one sample;
+// a 128-thread block stages its 128 feature rows in shared memory and writes them out as one
+// contiguous, fully coalesced 128*F*4-byte span.
+//
+// Roofline: HBM-bound in this staged form.  Algorithmic bytes per sample = 4F (row out) + 12 (ndc out)
+// + 4 (z in) = 4F+16, plus the maps once per frame (they are L2-resident: 62 MB at 320x256).
+#include "ucn_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 128;
+
+struct Acc8 { float v[8]; };
+
+__device__ __forceinline__ void fma8(Acc8 &a, const float *__restrict__ texel, float w) {
+  const float4 lo = ucn::ldg4(texel), hi = ucn::ldg4(texel + 4);
+  a.v[0] = fmaf(lo.x, w, a.v[0]); a.v[1] = fmaf(lo.y, w, a.v[1]);
+  a.v[2] = fmaf(lo.z, w, a.v[2]); a.v[3] = fmaf(lo.w, w, a.v[3]);
+  a.v[4] = fmaf(hi.x, w, a.v[4]); a.v[5] = fmaf(hi.y, w, a.v[5]);
+  a.v[6] = fmaf(hi.z, w, a.v[6]); a.v[7] = fmaf(hi.w, w, a.v[7]);
+}
+
+// trilinear, border padding, align_corners=False, over a [D][h][w][8] volume
+__device__ __forceinline__ void tri8(const float *__restrict__ vol, int D, int h, int w, float cx, float cy, float cz,
+                                     float *__restrict__ out, int32_t *__restrict__ idx) {
+  const ucn::Lerp1 ax = ucn::axis(ucn::to_grid(cx), w, false);
+  const ucn::Lerp1 ay = ucn::axis(ucn::to_grid(cy), h, false);
+  const ucn::Lerp1 az = ucn::axis(ucn::to_grid(cz), D, false);
+  if (idx) { idx[0] = ax.i0; idx[1] = ay.i0; idx[2] = az.i0; }
+  Acc8 a = {};
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const int dx = c & 1, dy = (c >> 1) & 1, dz = c >> 2;
+    if ((dx && !ax.has1) || (dy && !ay.has1) || (dz && !az.has1)) continue;
+    const float wgt = __fmul_rn(__fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0), dz ? az.w1 : az.w0);
+    const size_t t = ((size_t)(az.i0 + dz) * h + (ay.i0 + dy)) * w + (ax.i0 + dx);
+    fma8(a, vol + t * 8, wgt);
+  }
+#pragma unroll
+  for (int c = 0; c < 8; ++c) out[c] = a.v[c];
+}
+
+template <bool FROM_Z>
+__global__ void __launch_bounds__(kThreads)
+gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts_or_z,
+              const float *__restrict__ ndc1, const float *__restrict__ ndc2, const float *__restrict__ ndc3,
+              const float *__restrict__ pix_yx, int ray0, int R, int64_t n_samples, int parts,
+              float *__restrict__ feat, float *__restrict__ ndc_out, int32_t *__restrict__ idx_out) {
+  extern __shared__ float rows[];                       // [kThreads][F + 1]  (+1: odd stride, no bank conflicts)
+  const int V = f.V, F = 24 + 12 * V + 1, ld = F + 1;
+  const int64_t q = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  float *row = rows + (size_t)threadIdx.x * ld;
+  if (q < n_samples) {
+    const float iw = (float)(f.W - 1), ih = (float)(f.H - 1);
+    float p[3], c1[3], c2[3], c3[3];
+    if (FROM_Z) {
+      const int r = (int)(q / f.S);
+      float ys, xs, d[3], nr[3], fr[3], nx, ny, pz;
+      ucn::pixel_of_ray(f, pix_yx, ray0, R, r, ys, xs);
+      ucn::ray_dir(f, ys, xs, d);
+      ucn::stage_near_far(f, ys, xs, nr, fr);
+      const float zj = pts_or_z[q];
+      p[0] = __fadd_rn(f.c2w[3], __fmul_rn(zj, d[0]));
+      p[1] = __fadd_rn(f.c2w[7], __fmul_rn(zj, d[1]));
+      p[2] = __fadd_rn(f.c2w[11], __fmul_rn(zj, d[2]));
+      ucn::project(f.w2c, f.K, iw, ih, p, nx, ny, pz);
+      c1[0] = c2[0] = c3[0] = nx;
+      c1[1] = c2[1] = c3[1] = ny;
+      c1[2] = __fdiv_rn(__fsub_rn(pz, nr[0]), __fsub_rn(fr[0], nr[0]));
+      c2[2] = __fdiv_rn(__fsub_rn(pz, nr[1]), __fsub_rn(fr[1], nr[1]));
+      c3[2] = __fdiv_rn(__fsub_rn(pz, nr[2]), __fsub_rn(fr[2], nr[2]));
+      if (ndc_out) {
+        ndc_out[3 * q] = nx; ndc_out[3 * q + 1] = ny;
+        ndc_out[3 * q + 2] = __fdiv_rn(__fsub_rn(pz, f.near), __fsub_rn(f.far, f.near));
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        p[c] = pts_or_z[3 * q + c];
+        c1[c] = ndc1[3 * q + c]; c2[c] = ndc2[3 * q + c]; c3[c] = ndc3[3 * q + c];
+      }
+    }
+    int32_t *ir = idx_out ? idx_out + q * (11 + 3 * V) : nullptr;
+    if (parts != UCN_PART_ALL) {
+      for (int c = 0; c < F; ++c) row[c] = 0.0f;
+      if (ir) for (int c = 0; c < 11 + 3 * V; ++c) ir[c] = 0;
+    }
+    if (parts & UCN_PART_VOLUMES) {
+    tri8(f.vol[0], f.D[0], f.h[0], f.w[0], c1[0], c1[1], c1[2], row, ir);
+    tri8(f.vol[1], f.D[1], f.h[1], f.w[1], c2[0], c2[1], c2[2], row + 8, ir ? ir + 3 : nullptr);
+    tri8(f.vol[2], f.D[2], f.h[2], f.w[2], c3[0], c3[1], c3[2], row + 16, ir ? ir + 6 : nullptr);
+    {   // confidence: depth-1 "volume" => bilinear, align_corners=False (renderer.py:195, utils.py:859-865)
+      const ucn::Lerp1 ax = ucn::axis(ucn::to_grid(c3[0]), f.W, false), ay = ucn::axis(ucn::to_grid(c3[1]), f.H, false);
+      float acc = 0.0f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int dx = c & 1, dy = c >> 1;
+        if ((dx && !ax.has1) || (dy && !ay.has1)) continue;
+        acc = fmaf(__ldg(f.conf + (size_t)(ay.i0 + dy) * f.W + ax.i0 + dx),
+                   __fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0), acc);
+      }
+      row[F - 1] = acc;
+      if (ir) { ir[9] = ax.i0; ir[10] = ay.i0; }
+    }
+    }
+    const size_t HW = (size_t)f.H * f.W;
+    for (int v = 0; v < ((parts & UCN_PART_VIEWS) ? V : 0); ++v) {   // utils/utils.py:766-798
+      float nx, ny, pz;
+      ucn::project(f.src_w2c + 16 * v, f.src_K + 9 * v, iw, ih, p, nx, ny, pz);
+      const float gx = ucn::to_grid(nx), gy = ucn::to_grid(ny);
+      const ucn::Lerp1 ax = ucn::axis(gx, f.W, true), ay = ucn::axis(gy, f.H, true);
+      const float m = (gx > -1.0f && gx < 1.0f && gy > -1.0f && gy < 1.0f) ? 1.0f : 0.0f;
+      float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+      Acc8 a = {};
+      const float *rgb = f.rgb + (size_t)v * HW * 4, *ft = f.feat + (size_t)v * HW * 8;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int dx = k & 1, dy = k >> 1;
+        if ((dx && !ax.has1) || (dy && !ay.has1)) continue;
+        const float wgt = __fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0);
+        const size_t t = (size_t)(ay.i0 + dy) * f.W + ax.i0 + dx;
+        const float4 px = ucn::ldg4(rgb + t * 4);
+        c.x = fmaf(px.x, wgt, c.x); c.y = fmaf(px.y, wgt, c.y); c.z = fmaf(px.z, wgt, c.z);
+        fma8(a, ft + t * 8, wgt);
+      }
+      float *o = row + 24 + 4 * v;
+      o[0] = c.x; o[1] = c.y; o[2] = c.z; o[3] = m;
+      float *of = row + 24 + 4 * V + 8 * v;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) of[k] = a.v[k];
+      if (ir) { ir[11 + 3 * v] = ax.i0; ir[12 + 3 * v] = ay.i0; ir[13 + 3 * v] = (int32_t)m; }
+    }
+  }
+  __syncthreads();
+  // coalesced write-out of the block's contiguous [rows_here][F] span
+  const int64_t q0 = (int64_t)blockIdx.x * kThreads;
+  const int rows_here = (int)min((int64_t)kThreads, n_samples - q0);
+  float *dst = feat + q0 * F;
+  for (int e = threadIdx.x; e < rows_here * F; e += kThreads) dst[e] = rows[(e / F) * ld + e % F];
+}
+
+}  // namespace
+
+static int launch_gather(bool from_z, const ucn_frame *f, const float *a, const float *n1, const float *n2,
+                         const float *n3, const float *pix_yx, int ray0, int R, int64_t n, int parts,
+                         float *feat, float *ndc_out, int32_t *idx, void *stream) {
+  UCN_CHECK_ARG(f && a && feat, "ucn_gather: null argument");
+  UCN_CHECK_ARG(f->V >= 1 && f->V <= UCN_MAX_V, "ucn_gather: 1 <= V <= 8 source views");
+  if (n <= 0) return UCN_OK;
+  const int F = 24 + 12 * f->V + 1;
+  const size_t smem = (size_t)kThreads * (F + 1) * sizeof(float);
+  const unsigned blocks = (unsigned)((n + kThreads - 1) / kThreads);
+  if (from_z) {
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; }
+    gather_kernel<true><<<blocks, kThreads, smem, (cudaStream_t)stream>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts,
+                                                                         feat, ndc_out, idx);
+  } else {
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; }
+    gather_kernel<false><<<blocks, kThreads, smem, (cudaStream_t)stream>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts,
+                                                                          feat, ndc_out, idx);
+  }
+  UCN_LAUNCH_CHECK("gather_kernel");
+  return UCN_OK;
+}
+
+extern "C" int ucn_gather(const ucn_frame *f, const float *pts, const float *ndc_s1, const float *ndc_s2,
+                          const float *ndc_s3, int64_t n_samples, int parts, float *feat, int32_t *idx,
+                          void *stream) {
+  UCN_CHECK_ARG(ndc_s1 && ndc_s2 && ndc_s3, "ucn_gather: null ndc");
+  UCN_CHECK_ARG(parts >= 1 && parts <= 3, "ucn_gather: parts must be 1, 2 or 3");
+  return launch_gather(false, f, pts, ndc_s1, ndc_s2, ndc_s3, nullptr, 0, 0, n_samples, parts, feat, nullptr, idx,
+                       stream);
+}
+
+extern "C" int ucn_gather_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R,
+                                 float *feat, float *ndc_pts, void *stream) {
+  UCN_CHECK_ARG(f && f->S > 0, "ucn_gather_from_z: bad frame");
+  return launch_gather(true, f, z, nullptr, nullptr, nullptr, pix_yx, ray0, R, (int64_t)R * f->S, UCN_PART_ALL, feat,
+                       ndc_pts, nullptr, stream);
+}
+
+namespace {
+struct Cam { float w2c[16], K[9]; };
+__global__ void project_kernel(const __grid_constant__ Cam cam, float iw, float ih, const float *__restrict__ pts,
+                               int64_t n, float *__restrict__ out) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n) return;
+  const float p[3] = {pts[3 * q], pts[3 * q + 1], pts[3 * q + 2]};
+  float nx, ny, pz;
+  ucn::project(cam.w2c, cam.K, iw, ih, p, nx, ny, pz);
+  out[3 * q] = nx; out[3 * q + 1] = ny; out[3 * q + 2] = pz;
+}
+}  // namespace
+
+extern "C" int ucn_project_points(const float *w2c_host16, const float *K_host9, int H, int W, const float *pts,
+                                  int64_t n, float *out, void *stream) {
+  UCN_CHECK_ARG(w2c_host16 && K_host9 && pts && out, "ucn_project_points: null argument");
+  if (n <= 0) return UCN_OK;
+  Cam cam;
+  for (int i = 0; i < 16; ++i) cam.w2c[i] = w2c_host16[i];
+  for (int i = 0; i < 9; ++i) cam.K[i] = K_host9[i];
+  project_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(cam, (float)(W - 1), (float)(H - 1), pts, n, out);
+  UCN_LAUNCH_CHECK("project_kernel");
+  return UCN_OK;
+}

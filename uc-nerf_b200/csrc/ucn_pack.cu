@@ -1,0 +1,130 @@
+// ucn_pack.cu -- K0: relayout of the encoder's maps and of the MLP weights into kernel-friendly form.
+// Runs once per target view (maps) / once per weight load; HBM-bound, one pass over the data.
+//
+// The reference keeps NCDHW / NCHW maps and samples them with F.grid_sample, i.e. C channel-strided
+// 4-byte loads per texel (utils/utils.py:776-788,859-890).  Channels-last makes a texel one vector load.
+#include <limits.h>
+
+#include <cuda_bf16.h>
+
+#include "ucn_common.cuh"
+#include "ucn_weights.cuh"
+
+namespace {
+
+__global__ void pack_cl_kernel(const float *__restrict__ src, float *__restrict__ dst, int Cn, int64_t N, int Cpad,
+                               int64_t total) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // over B*N
+  if (i >= total) return;
+  const int64_t b = i / N, n = i - b * N;
+  const float *s = src + (b * Cn) * N + n;
+  float *d = dst + i * Cpad;
+  if (Cpad == 4) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    v.x = s[0];
+    if (Cn > 1) v.y = s[N];
+    if (Cn > 2) v.z = s[2 * N];
+    if (Cn > 3) v.w = s[3 * N];
+    *reinterpret_cast<float4 *>(d) = v;
+  } else if (Cpad == 8 && Cn == 8) {
+    float4 lo = make_float4(s[0], s[N], s[2 * N], s[3 * N]);
+    float4 hi = make_float4(s[4 * N], s[5 * N], s[6 * N], s[7 * N]);
+    reinterpret_cast<float4 *>(d)[0] = lo;
+    reinterpret_cast<float4 *>(d)[1] = hi;
+  } else {
+    for (int c = 0; c < Cpad; ++c) d[c] = c < Cn ? s[(int64_t)c * N] : 0.0f;
+  }
+}
+
+__global__ void pack_nearfar_kernel(const float *__restrict__ dv, float *__restrict__ dst, int D, int hw) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= hw) return;
+  reinterpret_cast<float2 *>(dst)[i] = make_float2(dv[i], dv[(size_t)(D - 1) * hw + i]);
+}
+
+// dst_f32[(row(k))*ldn + n_off + n] = src[n*K + k]; row(k) = (k >= shift_from ? k+1 : k) + k_off
+__global__ void pack_w_f32_kernel(const float *__restrict__ src, int Nout, int K, float *__restrict__ dst, int ldn,
+                                  int n_off, int k_off, int shift_from) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Nout * K) return;
+  const int n = i / K, k = i - n * K;
+  const int row = (k >= shift_from ? k + 1 : k) + k_off;
+  dst[(size_t)row * ldn + n_off + n] = src[i];
+}
+
+// UMMA interleaved K-major tile: element (n,k) -> ((k/8)*Ntile + n)*8 + k%8
+__global__ void pack_w_bf16_kernel(const float *__restrict__ src, int Nout, int K, __nv_bfloat16 *__restrict__ dst,
+                                   int Ntile, int n_off, int k_off, int shift_from) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Nout * K) return;
+  const int n = i / K + n_off, k0 = i % K;
+  const int k = (k0 >= shift_from ? k0 + 1 : k0) + k_off;
+  dst[((size_t)(k >> 3) * Ntile + n) * 8 + (k & 7)] = __float2bfloat16_rn(src[i]);
+}
+
+}  // namespace
+
+extern "C" int ucn_pack_channels_last(const float *src, float *dst, int B, int Cn, int64_t N, int Cpad, void *stream) {
+  UCN_CHECK_ARG(src && dst && B > 0 && Cn > 0 && N > 0 && Cpad >= Cn, "ucn_pack_channels_last: bad argument");
+  const int64_t total = (int64_t)B * N;
+  pack_cl_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(src, dst, Cn, N, Cpad, total);
+  UCN_LAUNCH_CHECK("pack_cl_kernel");
+  return UCN_OK;
+}
+
+extern "C" int ucn_pack_nearfar(const float *depth_values, float *dst, int D, int h, int w, void *stream) {
+  UCN_CHECK_ARG(depth_values && dst && D > 0 && h > 0 && w > 0, "ucn_pack_nearfar: bad argument");
+  pack_nearfar_kernel<<<(h * w + 255) / 256, 256, 0, (cudaStream_t)stream>>>(depth_values, dst, D, h * w);
+  UCN_LAUNCH_CHECK("pack_nearfar_kernel");
+  return UCN_OK;
+}
+
+extern "C" size_t ucn_weights_f32_bytes(int V) { return ucn::F32Layout(V).total * sizeof(float); }
+extern "C" size_t ucn_weights_bf16_bytes(int V) { return ucn::BF16Layout(V).total_bytes; }
+
+extern "C" int ucn_pack_weights(const ucn_state_dict *sd, float *dst, void *dst_bf16, void *stream_) {
+  UCN_CHECK_ARG(sd && (dst || dst_bf16), "ucn_pack_weights: null argument");
+  UCN_CHECK_ARG(sd->V >= 1 && sd->V <= UCN_MAX_V, "ucn_pack_weights: 1 <= V <= 8");
+  cudaStream_t st = (cudaStream_t)stream_;
+  const int V = sd->V;
+  const ucn::F32Layout L(V);
+  const ucn::BF16Layout B(V);
+  __nv_bfloat16 *hb = reinterpret_cast<__nv_bfloat16 *>(dst_bf16);
+  float *bias16 = dst_bf16 ? reinterpret_cast<float *>(reinterpret_cast<char *>(dst_bf16) + B.bias) : nullptr;
+  cudaError_t e;
+  if (dst && (e = cudaMemsetAsync(dst, 0, L.total * sizeof(float), st)) != cudaSuccess) return ucn_cuda_status(e, "memset f32 pack");
+  if (hb && (e = cudaMemsetAsync(hb, 0, B.total_bytes, st)) != cudaSuccess) return ucn_cuda_status(e, "memset bf16 pack");
+
+  auto mat = [&](const float *src, int Nout, int K, size_t off32, int ldn, size_t off16, int Ntile, int n_off,
+                 int k_off, int shift_from) {
+    const int n = Nout * K, blocks = (n + 255) / 256;
+    if (dst) { pack_w_f32_kernel<<<blocks, 256, 0, st>>>(src, Nout, K, dst + off32, ldn, n_off, k_off, shift_from); ucn_count_launch(); }
+    if (hb) {
+      pack_w_bf16_kernel<<<blocks, 256, 0, st>>>(src, Nout, K, reinterpret_cast<__nv_bfloat16 *>(reinterpret_cast<char *>(hb) + off16),
+                                                 Ntile, n_off, k_off, shift_from);
+      ucn_count_launch();
+    }
+  };
+  auto vec = [&](const float *src, int n, size_t off32, size_t off16) {
+    if (dst) cudaMemcpyAsync(dst + off32, src, n * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    if (bias16) cudaMemcpyAsync(bias16 + off16, src, n * sizeof(float), cudaMemcpyDeviceToDevice, st);
+  };
+  const int NS = INT_MAX;
+  mat(sd->film_w, 128, 24 + 4 * V, L.film, 128, B.film, 128, 0, 0, NS);  vec(sd->film_b, 128, L.film_b, B.b_film);
+  mat(sd->fb_w, 128, 8 * V, L.fb, 128, B.fb, 128, 0, 0, NS);              vec(sd->fb_b, 128, L.fb_b, B.b_fb);
+  for (int i = 0; i < 6; ++i) {
+    const int K = i == 0 ? 63 : (i == 5 ? 191 : 128);
+    mat(sd->pts_w[i], 128, K, L.pts[i], 128, B.pts[i], 128, 0, 0, i == 5 ? 63 : NS);
+    vec(sd->pts_b[i], 128, L.pts_b[i], B.b_pts[i]);
+  }
+  mat(sd->feature_w, 128, 128, L.feat, 128, B.feat, 128, 0, 0, NS);       vec(sd->feature_b, 128, L.feat_b, B.b_feat);
+  mat(sd->views_w, 64, 155, L.vv, 128, B.vv, 128, 0, 0, NS);              vec(sd->views_b, 64, L.vv_b, B.b_vv);
+  mat(sd->vconf_w, 64, 155, L.vv, 128, B.vv, 128, 64, 0, NS);             vec(sd->vconf_b, 64, L.vv_b + 64, B.b_vv + 64);
+  mat(sd->crgb_w, 3, 128, L.base, 4, B.base, 16, 0, 0, NS);               vec(sd->crgb_b, 3, L.base_b, B.b_base);
+  mat(sd->alpha1_w, 1, 128, L.base, 4, B.base, 16, 3, 0, NS);             vec(sd->alpha1_b, 1, L.base_b + 3, B.b_base + 3);
+  mat(sd->rgb_w, 3, 64, L.adapt, 4, B.adapt, 16, 0, 0, NS);               vec(sd->rgb_b, 3, L.adapt_b, B.b_adapt);
+  mat(sd->alpha_w, 1, 64, L.adapt, 4, B.adapt, 16, 3, 64, NS);            vec(sd->alpha_b, 1, L.adapt_b + 3, B.b_adapt + 3);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_pack_weights");
+  return UCN_OK;
+}

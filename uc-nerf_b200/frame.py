@@ -1,0 +1,270 @@
+"""Device-resident packed state for one target view, packed MLP weights, and the whole-frame entry
+point ``render_frame`` that replaces the reference's per-chunk Python loop (train.py:251-275).
+
+PyTorch is used for device memory and streams only; all arithmetic happens in libucnerf.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import lib as L
+
+STAGES = ("stage1", "stage2", "stage3")
+
+
+def _host(x, shape=None) -> np.ndarray:
+    if isinstance(x, torch.Tensor):
+        x = x.detach().to("cpu", torch.float32).numpy()
+    a = np.ascontiguousarray(np.asarray(x, dtype=np.float32))
+    return a if shape is None else a.reshape(shape)
+
+
+def _dev(x, device) -> torch.Tensor:
+    if isinstance(x, np.ndarray):
+        x = torch.from_numpy(np.ascontiguousarray(x))
+    return x.to(device=device, dtype=torch.float32).contiguous()
+
+
+def linspace01(n: int, device) -> torch.Tensor:
+    """t_vals exactly as the reference builds them: torch.linspace on the CPU, then .to(device)
+    (utils/utils.py:394)."""
+    return torch.linspace(0., 1., steps=n).to(device)
+
+
+class PackedFrame:
+    """Cameras (by value) + packed maps (device) for one target view == one ``ucn_frame``."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise L.UcnError("PackedFrame needs a CUDA device: there is no CPU path")
+        L.load()
+        self.c = L.Frame()
+        self._keep: Dict[str, torch.Tensor] = {}
+        self._t_vals: Optional[torch.Tensor] = None
+
+    # ---- cameras ----------------------------------------------------------------------------
+    def set_target(self, H, W, S, intrinsic, c2w, w2c, near, far, dir_rot0=None, dir_rot1=None, dir_switch=None):
+        if S % 3 != 0 or S <= 0 or S > L.UCN_MAX_S:
+            raise L.UcnError(f"N_samples={S}: must be a positive multiple of 3 (<= {L.UCN_MAX_S}); the reference "
+                             "itself fails for other values (utils/utils.py:666,707-712)")
+        c = self.c
+        c.H, c.W, c.S = int(H), int(W), int(S)
+        K = _host(intrinsic)
+        if K.ndim == 3:                      # reference: intrinsic.mean(0) when batched (utils/utils.py:638)
+            K = K.mean(0)
+        c.K[:] = K.reshape(-1).tolist()
+        c.c2w[:] = _host(c2w, (4, 4)).reshape(-1).tolist()
+        w2c = _host(w2c, (4, 4))
+        c.w2c[:] = w2c.reshape(-1).tolist()
+        c.near, c.far = float(near), float(far)
+        r0 = w2c[:3, :3] if dir_rot0 is None else _host(dir_rot0)[:3, :3]
+        r1 = r0 if dir_rot1 is None else _host(dir_rot1)[:3, :3]
+        c.dir_rot0[:] = np.ascontiguousarray(r0).reshape(-1).tolist()
+        c.dir_rot1[:] = np.ascontiguousarray(r1).reshape(-1).tolist()
+        c.dir_switch = int(2 ** 31 - 1 if dir_switch is None else dir_switch)
+        self._t_vals = linspace01(S // 3, self.device)
+        return self
+
+    def set_sources(self, w2cs, intrinsics):
+        w2cs, Ks = _host(w2cs), _host(intrinsics)
+        V = w2cs.shape[0]
+        if not 1 <= V <= L.UCN_MAX_V:
+            raise L.UcnError(f"{V} source views: supported range is 1..{L.UCN_MAX_V}")
+        self.c.V = V
+        self.c.src_w2c[:V * 16] = w2cs.reshape(-1).tolist()
+        self.c.src_K[:V * 9] = Ks.reshape(-1).tolist()
+        return self
+
+    # ---- maps ------------------------------------------------------------------------------
+    def _alloc(self, name, *shape):
+        t = torch.empty(shape, device=self.device, dtype=torch.float32)
+        self._keep[name] = t
+        return t
+
+    def pack_depth_values(self, depth_values: Sequence):
+        """outputs['stageK']['depth_values'] [1,D,h,w] -> [h,w,2] (first/last plane)."""
+        lib, st = L.load(), L.stream_ptr()
+        for k, dv in enumerate(depth_values):
+            dv = _dev(dv, self.device)
+            dv = dv[0] if dv.dim() == 4 else dv
+            D, h, w = dv.shape
+            self.c.D[k], self.c.h[k], self.c.w[k] = D, h, w
+            dst = self._alloc(f"nearfar{k}", h, w, 2)
+            L.check(lib.ucn_pack_nearfar(L.ptr(dv.contiguous()), L.ptr(dst), D, h, w, st), "ucn_pack_nearfar")
+            self.c.nearfar[k] = dst.data_ptr()
+        return self
+
+    def pack_volumes(self, volumes: Sequence):
+        """outputs['stageK']['volume_feature_no_ref'] [1,8,D,h,w] -> [D,h,w,8]."""
+        lib, st = L.load(), L.stream_ptr()
+        for k, vol in enumerate(volumes):
+            vol = _dev(vol, self.device)
+            vol = vol[0] if vol.dim() == 5 else vol
+            Cn, D, h, w = vol.shape
+            if Cn != 8:
+                raise L.UcnError("feature volumes must have 8 channels")
+            if self.c.D[k] and (self.c.D[k], self.c.h[k], self.c.w[k]) != (D, h, w):
+                raise L.UcnError("volume / depth_values shape mismatch")
+            self.c.D[k], self.c.h[k], self.c.w[k] = D, h, w
+            dst = self._alloc(f"vol{k}", D, h, w, 8)
+            L.check(lib.ucn_pack_channels_last(L.ptr(vol.contiguous()), L.ptr(dst), 1, 8, D * h * w, 8, st),
+                    "ucn_pack_channels_last(volume)")
+            self.c.vol[k] = dst.data_ptr()
+        return self
+
+    def pack_sources(self, imgs, img_feat, confidence):
+        """imgs [1,V,3,H,W] -> [V,H,W,4]; img_feat [V,1,8,H,W] -> [V,H,W,8]; confidence [1,H,W] as is."""
+        lib, st = L.load(), L.stream_ptr()
+        imgs = _dev(imgs, self.device)
+        imgs = imgs[0] if imgs.dim() == 5 else imgs
+        V, C3, H, W = imgs.shape
+        feat = _dev(img_feat, self.device).reshape(V, 8, H, W)
+        conf = _dev(confidence, self.device).reshape(H, W)
+        rgb = self._alloc("rgb", V, H, W, 4)
+        ft = self._alloc("feat", V, H, W, 8)
+        L.check(lib.ucn_pack_channels_last(L.ptr(imgs.contiguous()), L.ptr(rgb), V, C3, H * W, 4, st), "pack rgb")
+        L.check(lib.ucn_pack_channels_last(L.ptr(feat), L.ptr(ft), V, 8, H * W, 8, st), "pack feat")
+        self._keep["conf"] = conf
+        self.c.rgb, self.c.feat, self.c.conf = rgb.data_ptr(), ft.data_ptr(), conf.data_ptr()
+        return self
+
+    @property
+    def t_vals(self) -> torch.Tensor:
+        return self._t_vals
+
+    @property
+    def F(self) -> int:
+        return 24 + 12 * self.c.V + 1
+
+    @property
+    def map_bytes(self) -> int:
+        return sum(t.numel() * 4 for t in self._keep.values())
+
+    # ---- convenience ----------------------------------------------------------------------
+    @classmethod
+    def from_scene(cls, scene, S: int, device="cuda", dir_switch: Optional[int] = None, quirk_q4: bool = True):
+        """Build from a synthetic.Scene (numpy, reference layouts)."""
+        f = cls(device)
+        f.set_target(scene.H, scene.W, S, scene.K[0], scene.c2ws[0], scene.w2cs[0], scene.near_fars[0, 0],
+                     scene.near_fars[0, 1], dir_rot0=scene.w2cs[0],
+                     dir_rot1=scene.w2cs[1] if quirk_q4 else scene.w2cs[0],
+                     dir_switch=1024 if dir_switch is None else dir_switch)   # opt.py:65 default chunk
+        f.set_sources(scene.w2cs[1:], scene.K[1:])
+        f.pack_depth_values(scene.depth_values)
+        if scene.volumes:
+            f.pack_volumes(scene.volumes)
+            f.pack_sources(scene.imgs, scene.img_feats, scene.confidence)
+        return f
+
+
+_SD_FIELDS = (("film", "pts_bias_depth_fine"), ("fb", "pts_bias_confidence"), ("feature", "feature_linear"),
+              ("views", "views_linears.0"), ("vconf", "view_confi_linears.0"), ("rgb", "rgb_linear"),
+              ("alpha", "alpha_linear"), ("crgb", "confi_rgb_linear"), ("alpha1", "alpha_linear_1"))
+
+
+class PackedWeights:
+    """fp32 + bf16 kernel packs of a UC-NeRF state_dict (reference key names, network/models.py:87-104)."""
+
+    def __init__(self, state_dict: Dict, V: int, device="cuda"):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise L.UcnError("PackedWeights needs a CUDA device: there is no CPU path")
+        lib = L.load()
+        sd = {k: _dev(v, self.device) for k, v in state_dict.items()}
+        exp = {"nerf.pts_linears.0.weight": (128, 63), "nerf.pts_linears.5.weight": (128, 191),
+               "nerf.pts_bias_depth_fine.weight": (128, 24 + 4 * V), "nerf.pts_bias_confidence.weight": (128, 8 * V),
+               "nerf.views_linears.0.weight": (64, 155)}
+        for k, shp in exp.items():
+            if tuple(sd[k].shape) != shp:
+                raise L.UcnError(f"{k}: shape {tuple(sd[k].shape)} != {shp}; only D=6, W=128, multires=10/4, skips=[4] "
+                                 "(the reference defaults, opt.py:40-44,90-92) are supported")
+        c = L.StateDict()
+        c.V = V
+        for i in range(6):
+            c.pts_w[i] = sd[f"nerf.pts_linears.{i}.weight"].data_ptr()
+            c.pts_b[i] = sd[f"nerf.pts_linears.{i}.bias"].data_ptr()
+        for field, name in _SD_FIELDS:
+            setattr(c, field + "_w", sd[f"nerf.{name}.weight"].data_ptr())
+            setattr(c, field + "_b", sd[f"nerf.{name}.bias"].data_ptr())
+        self.f32 = torch.empty(lib.ucn_weights_f32_bytes(V) // 4, device=self.device, dtype=torch.float32)
+        self.bf16 = torch.empty(lib.ucn_weights_bf16_bytes(V), device=self.device, dtype=torch.uint8)
+        L.check(lib.ucn_pack_weights(C.byref(c), L.ptr(self.f32), L.ptr(self.bf16), L.stream_ptr()), "ucn_pack_weights")
+        torch.cuda.current_stream().synchronize()      # sd temporaries may be freed after this
+        self.c = L.Weights()
+        self.c.V, self.c.f32, self.c.bf16 = V, self.f32.data_ptr(), self.bf16.data_ptr()
+        self.V = V
+
+
+class FrameRenderer:
+    """Whole-frame renderer: owns the workspace, runs K1->K2->K3->K4 on the current stream."""
+
+    def __init__(self, frame: PackedFrame, weights: PackedWeights, mode: str = "bf16", max_rays: Optional[int] = None):
+        self.frame, self.weights, self.mode = frame, weights, L.MODES[mode]
+        self.lib = L.load()
+        L.check(self.lib.ucn_check_device(), "ucn_check_device")
+        self.max_rays = int(max_rays or frame.c.H * frame.c.W)
+        self.ws_bytes = int(self.lib.ucn_frame_workspace_bytes(C.byref(frame.c), self.max_rays, self.mode))
+        self.ws = torch.empty(self.ws_bytes, device=frame.device, dtype=torch.uint8)
+
+    def render(self, ray0: int = 0, n_rays: Optional[int] = None, t_rand: Optional[torch.Tensor] = None, seed: int = 0,
+               out_rgb: Optional[torch.Tensor] = None, out_depth: Optional[torch.Tensor] = None,
+               timers: Optional[dict] = None):
+        f = self.frame
+        total = f.c.H * f.c.W
+        n = total - ray0 if n_rays is None else int(n_rays)
+        rgb = out_rgb if out_rgb is not None else torch.empty((n, 3), device=f.device, dtype=torch.float32)
+        depth = out_depth if out_depth is not None else torch.empty((n,), device=f.device, dtype=torch.float32)
+        for lo in range(0, n, self.max_rays):
+            m = min(self.max_rays, n - lo)
+            tr = None if t_rand is None else t_rand[lo:lo + m]
+            if timers is None:
+                L.check(self.lib.ucn_render_rays(C.byref(f.c), C.byref(self.weights.c), ray0 + lo, m, L.ptr(f.t_vals),
+                                                 L.ptr(tr), int(seed), self.mode, L.ptr(self.ws), self.ws_bytes,
+                                                 L.ptr(rgb[lo:lo + m]), L.ptr(depth[lo:lo + m]), L.stream_ptr()),
+                        "ucn_render_rays")
+            else:
+                self._render_staged(ray0 + lo, m, tr, seed, rgb[lo:lo + m], depth[lo:lo + m], timers)
+        return rgb, depth
+
+    def _carve(self, m):
+        """Workspace views with the same order ucn_render_rays uses (z, rays_d, angle, ndc, feat, raw)."""
+        S, F = self.frame.c.S, self.frame.F
+        out, o = [], 0
+        for shape in ((m, S), (m, 3), (m, 3), (m, S, 3), (m, S, F), (m, S, 4)):
+            nbytes = 4 * int(np.prod(shape))
+            out.append(self.ws[o:o + nbytes].view(torch.float32).view(*shape))
+            o += (nbytes + 255) & ~255
+        return out
+
+    def _render_staged(self, ray0, m, t_rand, seed, rgb, depth, timers):
+        """Same five launches as ucn_render_rays, issued one by one so that CUDA events on the launching
+        stream can bracket each kernel (bench.py's roofline measurement)."""
+        f, lib, st = self.frame, self.lib, L.stream_ptr()
+        z, rays_d, angle, ndc, feat, raw = self._carve(m)
+
+        def timed(name, fn):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            timers.setdefault(name, []).append((e0, e1))
+        timed("raygen", lambda: L.check(lib.ucn_raygen_sample(C.byref(f.c), None, ray0, m, L.ptr(f.t_vals), L.ptr(t_rand),
+                                                              int(seed), L.ptr(z), L.ptr(rays_d), None, None, st), "K1"))
+        timed("dir", lambda: L.check(lib.ucn_dir_feature(C.byref(f.c), L.ptr(rays_d), m, ray0, L.ptr(angle), st), "dir"))
+        timed("gather", lambda: L.check(lib.ucn_gather_from_z(C.byref(f.c), L.ptr(z), None, ray0, m, L.ptr(feat),
+                                                              L.ptr(ndc), st), "K2"))
+        timed("mlp", lambda: L.check(lib.ucn_mlp_forward(C.byref(self.weights.c), L.ptr(ndc), L.ptr(feat), L.ptr(angle),
+                                                         m, f.c.S, L.ptr(raw), self.mode, st), "K3"))
+        timed("composite", lambda: L.check(lib.ucn_composite(L.ptr(raw), L.ptr(z), m, f.c.S, 0, L.ptr(rgb), L.ptr(depth),
+                                                             None, None, st), "K4"))
+
+
+def render_frame(frame: PackedFrame, weights: PackedWeights, mode: str = "bf16", t_rand=None, seed: int = 0,
+                 ray0: int = 0, n_rays: Optional[int] = None, max_rays: Optional[int] = None):
+    """One call per target view: (rgb [R,3], depth [R]) for rays ray0..ray0+R of the row-major pixel grid."""
+    return FrameRenderer(frame, weights, mode, max_rays).render(ray0, n_rays, t_rand, seed)

@@ -1,0 +1,115 @@
+"""ctypes binding of libucnerf.so (include/ucnerf.h).  Fails loudly: no library, no product."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libucnerf.so")
+
+UCN_MAX_V = 8
+UCN_MAX_S = 1024
+MLP_FP32, MLP_BF16_TC = 0, 1
+PART_VOLUMES, PART_VIEWS, PART_ALL = 1, 2, 3
+MODES = {"fp32": MLP_FP32, "bf16": MLP_BF16_TC}
+
+_fp = C.c_void_p
+
+
+class Frame(C.Structure):
+    _fields_ = [("H", C.c_int32), ("W", C.c_int32), ("V", C.c_int32), ("S", C.c_int32),
+                ("D", C.c_int32 * 3), ("h", C.c_int32 * 3), ("w", C.c_int32 * 3),
+                ("K", C.c_float * 9), ("c2w", C.c_float * 16), ("w2c", C.c_float * 16),
+                ("near", C.c_float), ("far", C.c_float),
+                ("dir_rot0", C.c_float * 9), ("dir_rot1", C.c_float * 9),
+                ("dir_switch", C.c_int32), ("reserved", C.c_int32),
+                ("src_w2c", C.c_float * (UCN_MAX_V * 16)), ("src_K", C.c_float * (UCN_MAX_V * 9)),
+                ("nearfar", _fp * 3), ("vol", _fp * 3), ("conf", _fp), ("rgb", _fp), ("feat", _fp)]
+
+
+class Weights(C.Structure):
+    _fields_ = [("V", C.c_int32), ("reserved", C.c_int32), ("f32", _fp), ("bf16", _fp)]
+
+
+class StateDict(C.Structure):
+    _fields_ = [("V", C.c_int32), ("reserved", C.c_int32), ("pts_w", _fp * 6), ("pts_b", _fp * 6)] + [
+        (n + s, _fp) for n in ("film", "fb", "feature", "views", "vconf", "rgb", "alpha", "crgb", "alpha1")
+        for s in ("_w", "_b")]
+
+
+class UcnError(RuntimeError):
+    pass
+
+
+_lib = None
+
+_SIGS = {
+    "ucn_version": (C.c_int, []),
+    "ucn_last_error": (C.c_char_p, []),
+    "ucn_launch_count": (C.c_int64, [C.c_int]),
+    "ucn_check_device": (C.c_int, []),
+    "ucn_pack_channels_last": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int64, C.c_int, _fp]),
+    "ucn_pack_nearfar": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp]),
+    "ucn_weights_f32_bytes": (C.c_size_t, [C.c_int]),
+    "ucn_weights_bf16_bytes": (C.c_size_t, [C.c_int]),
+    "ucn_pack_weights": (C.c_int, [C.POINTER(StateDict), _fp, _fp, _fp]),
+    "ucn_raygen_sample": (C.c_int, [C.POINTER(Frame), _fp, C.c_int, C.c_int, _fp, _fp, C.c_uint64, _fp, _fp, _fp,
+                                    _fp, _fp]),
+    "ucn_gather": (C.c_int, [C.POINTER(Frame), _fp, _fp, _fp, _fp, C.c_int64, C.c_int, _fp, _fp, _fp]),
+    "ucn_project_points": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_int, C.c_int, _fp, C.c_int64,
+                                     _fp, _fp]),
+    "ucn_gather_from_z": (C.c_int, [C.POINTER(Frame), _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp]),
+    "ucn_dir_feature": (C.c_int, [C.POINTER(Frame), _fp, C.c_int, C.c_int, _fp, _fp]),
+    "ucn_mlp_forward": (C.c_int, [C.POINTER(Weights), _fp, _fp, _fp, C.c_int, C.c_int, _fp, C.c_int, _fp]),
+    "ucn_composite": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, _fp]),
+    "ucn_frame_workspace_bytes": (C.c_size_t, [C.POINTER(Frame), C.c_int, C.c_int]),
+    "ucn_render_rays": (C.c_int, [C.POINTER(Frame), C.POINTER(Weights), C.c_int, C.c_int, _fp, _fp, C.c_uint64,
+                                  C.c_int, _fp, C.c_size_t, _fp, _fp, _fp]),
+}
+
+
+def exported_symbols():
+    """Every symbol include/ucnerf.h declares (used by the CPU-side ABI test)."""
+    return sorted(_SIGS)
+
+
+def load():
+    """dlopen libucnerf.so and attach signatures.  Raises if the extension is missing: there is no
+    CPU or PyTorch fallback anywhere in this package."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise UcnError(f"{LIB_PATH} not built -- run `python -m ucnerf_b200.build` (no fallback path exists)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in _SIGS.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        msg = load().ucn_last_error().decode(errors="replace")
+        raise UcnError(f"{what or 'libucnerf'} failed (code {rc}): {msg}")
+
+
+def ptr(t):
+    """Device pointer of a contiguous fp32/int32 CUDA tensor (or None)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise UcnError("libucnerf has no CPU path: tensor must live on a CUDA device")
+    if not t.is_contiguous():
+        raise UcnError("tensor must be contiguous")
+    return C.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def launch_count(reset: bool = False) -> int:
+    return int(load().ucn_launch_count(1 if reset else 0))

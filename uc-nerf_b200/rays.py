@@ -1,0 +1,226 @@
+"""Drop-in mirrors of the reference's ray / sampling / gather helpers, backed by libucnerf.so.
+
+Same names, argument order, return tuples and tensor shapes as the reference functions:
+
+    utils/utils.py:217   get_rays_mvs            utils/utils.py:600   build_rays_test
+    utils/utils.py:323   get_ndc_coordinate      utils/utils.py:393   sample_points_uniform
+    utils/utils.py:742   build_color_volume      utils/utils.py:833   index_point_feature
+    data/ray_utils.py:12 get_ray_directions      data/ray_utils.py:32 get_rays
+
+Everything runs on the tensors' CUDA device; there is no CPU path (``use_cpu=True`` raises).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import torch
+
+from . import lib as L
+from .frame import PackedFrame, linspace01
+
+_FRAME_CACHE: Dict[tuple, PackedFrame] = {}
+_CACHE_MAX = 8
+
+
+def _key(*tensors):
+    return tuple((t.data_ptr(), t._version, tuple(t.shape)) if isinstance(t, torch.Tensor) else t for t in tensors)
+
+
+def _cache_put(key, val):
+    if len(_FRAME_CACHE) >= _CACHE_MAX:
+        _FRAME_CACHE.pop(next(iter(_FRAME_CACHE)))
+    _FRAME_CACHE[key] = val
+    return val
+
+
+def _need_cuda(t: torch.Tensor, what: str):
+    if not t.is_cuda:
+        raise L.UcnError(f"{what}: tensors must be on a CUDA device (no CPU fallback exists)")
+
+
+def sample_points_uniform(device, near, far, num_samples, num_rays):
+    """utils/utils.py:393-397 (elementwise torch ops; kept for API completeness, K1 fuses it)."""
+    t_vals = linspace01(num_samples, device).view(1, num_samples).expand(num_rays, num_samples)
+    return near * (1.0 - t_vals) + far * t_vals
+
+
+def _rays_frame(H, W, S, tgt_to_world, world_to_ref, intrinsic, near, far, outputs) -> PackedFrame:
+    dvs = [outputs[s]["depth_values"] for s in ("stage1", "stage2", "stage3")]
+    key = ("rays", H, W, S, float(near), float(far)) + _key(tgt_to_world, world_to_ref, intrinsic, *dvs)
+    fr = _FRAME_CACHE.get(key)
+    if fr is None:
+        fr = PackedFrame(tgt_to_world.device)
+        fr.set_target(H, W, S, intrinsic, tgt_to_world, world_to_ref, near, far)
+        fr.pack_depth_values(dvs)
+        _cache_put(key, fr)
+    return fr
+
+
+def build_rays_test(H, W, tgt_to_world, world_to_ref, intrinsic, near_fars_ref, near_fars, N_samples, pad=0,
+                    ref_idx=0, use_cpu=False, chunk=-1, idx=-1, outputs=None, t_rand: Optional[torch.Tensor] = None,
+                    seed: int = 0):
+    """utils/utils.py:600-739.  Returns (ray_coordinate_world [R,S,3], ray_dir_world [R,3],
+    ray_coordinate_ref {stage1,stage2,stage3,ndc: [R,S,3]}, depth_candidates [R,S], rays_os [R,3], ndc_parameters).
+
+    ``t_rand`` ([R,S] uniforms) is the one extension: the reference draws ``torch.rand`` internally
+    (:705); pass it to reproduce a given draw, omit it for the in-kernel Philox stream keyed by ``seed``."""
+    if use_cpu:
+        raise L.UcnError("build_rays_test(use_cpu=True): no CPU path in this implementation")
+    _need_cuda(tgt_to_world, "build_rays_test")
+    device = tgt_to_world.device
+    S = int(N_samples)
+    near, far = near_fars_ref[ref_idx, 0], near_fars_ref[ref_idx, 1]
+    fr = _rays_frame(int(H), int(W), S, tgt_to_world, world_to_ref, intrinsic, float(near), float(far), outputs)
+    total = H * W
+    lo, hi = (0, total) if chunk <= 0 else (idx * chunk, min(total, (idx + 1) * chunk))
+    R = hi - lo
+    z = torch.empty((R, S), device=device)
+    rays_d = torch.empty((R, 3), device=device)
+    pts = torch.empty((R, S, 3), device=device)
+    ndc = torch.empty((4, R, S, 3), device=device)
+    if t_rand is not None:
+        t_rand = t_rand.to(device=device, dtype=torch.float32).contiguous()
+        assert tuple(t_rand.shape) == (R, S)
+    L.check(L.load().ucn_raygen_sample(C.byref(fr.c), None, lo, R, L.ptr(fr.t_vals), L.ptr(t_rand), int(seed),
+                                       L.ptr(z), L.ptr(rays_d), L.ptr(pts), L.ptr(ndc), L.stream_ptr()),
+            "ucn_raygen_sample")
+    rays_o = tgt_to_world[:3, -1].clone().reshape(1, 3).expand(R, -1)
+    inv_scale = torch.tensor([W - 1, H - 1]).to(device)
+    ndc_parameters = {"w2c_ref": world_to_ref, "intrinsic_ref": intrinsic, "inv_scale": inv_scale, "near": near,
+                      "far": far, "pad": pad}
+    rays_ndc = {"stage1": ndc[0], "stage2": ndc[1], "stage3": ndc[2], "ndc": ndc[3]}
+    return pts, rays_d, rays_ndc, z, rays_o, ndc_parameters
+
+
+def get_rays_mvs(H, W, intrinsic, c2w, N=1024, isRandom=True, is_precrop_iters=False, chunk=-1, idx=-1,
+                 with_mask=False, photo_confidence=None):
+    """utils/utils.py:217-271, eval branch (isRandom=False): -> (rays_o [3], rays_d [R,3], pixel_coordinates [2,R])."""
+    if isRandom:
+        raise L.UcnError("get_rays_mvs(isRandom=True): ray *selection* stays in PyTorch; use get_rays_for_pixels")
+    total = H * W
+    lo, hi = (0, total) if chunk <= 0 else (idx * chunk, min(total, (idx + 1) * chunk))
+    g = torch.arange(lo, hi, device=c2w.device)
+    ys, xs = torch.div(g, W, rounding_mode="floor").float(), (g % W).float()
+    return get_rays_for_pixels(H, W, intrinsic, c2w, ys, xs)
+
+
+def get_rays_for_pixels(H, W, intrinsic, c2w, ys, xs):
+    """Shared tail of get_rays_mvs / get_rays_mvs_coord (utils/utils.py:259-271, 304-320) for explicit pixels."""
+    _need_cuda(c2w, "get_rays")
+    device, R = c2w.device, ys.numel()
+    fr = PackedFrame(device)
+    eye = torch.eye(4)
+    fr.set_target(H, W, 3, intrinsic, c2w, eye, 0.0, 1.0)
+    # K1 needs near/far maps; a 1x1 dummy per stage keeps the kernel shape-agnostic for this ray-only use
+    dummy = [torch.zeros((1, 2, max(H // d, 1), max(W // d, 1)), device=device) for d in (4, 2, 1)]
+    fr.pack_depth_values(dummy)
+    pix = torch.stack((ys.float(), xs.float())).contiguous()
+    z = torch.empty((R, 3), device=device)
+    rays_d = torch.empty((R, 3), device=device)
+    tr = torch.zeros((R, 3), device=device)
+    L.check(L.load().ucn_raygen_sample(C.byref(fr.c), L.ptr(pix), 0, R, L.ptr(fr.t_vals), L.ptr(tr), 0, L.ptr(z),
+                                       L.ptr(rays_d), None, None, L.stream_ptr()), "ucn_raygen_sample")
+    return c2w[:3, -1].clone(), rays_d, pix
+
+
+def get_ray_directions(H, W, focal, center=None):
+    """data/ray_utils.py:12-29: camera-frame directions [H,W,3] (x right, y down, z forward)."""
+    device = focal.device if isinstance(focal, torch.Tensor) else "cuda"
+    cx, cy = (W / 2, H / 2) if center is None else center
+    K = torch.tensor([[float(focal[0]) if hasattr(focal, "__len__") else float(focal), 0, cx],
+                      [0, float(focal[1]) if hasattr(focal, "__len__") else float(focal), cy], [0, 0, 1]])
+    _, d, _ = get_rays_mvs(H, W, K, torch.eye(4, device=device), isRandom=False)
+    return d.reshape(H, W, 3)
+
+
+def get_rays(directions, c2w):
+    """data/ray_utils.py:32-53: rotate camera-frame directions into the world; -> (rays_o [N,3], rays_d [N,3])."""
+    rays_d = directions.reshape(-1, 3) @ c2w[:3, :3].T
+    rays_o = c2w[:3, 3].expand(rays_d.shape)
+    return rays_o, rays_d
+
+
+def get_ndc_coordinate(w2c_ref, intrinsic_ref, point_samples, inv_scale, near_far=None, sample_2d=False):
+    """utils/utils.py:323-373.  point_samples [R,S,3] -> [R,S,3] (sample_2d) or the 4-entry dict."""
+    _need_cuda(point_samples, "get_ndc_coordinate")
+    R, S = point_samples.shape[:2]
+    pts = point_samples.to(torch.float32).contiguous()
+    out = torch.empty((R, S, 3), device=pts.device)
+    w2c = (C.c_float * 16)(*torch.as_tensor(w2c_ref).detach().float().cpu().reshape(-1).tolist())
+    K = (C.c_float * 9)(*torch.as_tensor(intrinsic_ref).detach().float().cpu().reshape(-1).tolist())
+    Wm1, Hm1 = (int(v) for v in torch.as_tensor(inv_scale).reshape(-1).tolist())
+    L.check(L.load().ucn_project_points(w2c, K, Hm1 + 1, Wm1 + 1, L.ptr(pts), R * S, L.ptr(out), L.stream_ptr()),
+            "ucn_project_points")
+    if sample_2d:
+        return out
+    xy, pz = out[..., :2], out[..., 2:]
+    res = {}
+    for name, nk, fk in (("stage1", "near_1", "far_1"), ("stage2", "near_2", "far_2"), ("stage3", "near_3", "far_3"),
+                         ("ndc", "near", "far")):
+        res[name] = torch.cat([xy, (pz - near_far[nk]) / (near_far[fk] - near_far[nk])], dim=-1)
+    return res
+
+
+def _maps_frame(volume_feature, imgs, img_feat, confidence, pose_ref) -> PackedFrame:
+    """Packed maps for (volumes, images, features, confidence, source cameras); any group may be None."""
+    vols = None if volume_feature is None else [volume_feature[s]["volume_feature_no_ref"]
+                                                for s in ("stage1", "stage2", "stage3")]
+    cams = () if pose_ref is None else (pose_ref["w2cs"], pose_ref["intrinsics"])
+    key = ("maps",) + _key(imgs, img_feat, confidence, *cams, *(vols or ()))
+    fr = _FRAME_CACHE.get(key)
+    if fr is None:
+        ref = imgs if imgs is not None else confidence
+        fr = PackedFrame(ref.device)
+        H, W = ref.shape[-2:]
+        fr.c.H, fr.c.W, fr.c.S = int(H), int(W), 3
+        if vols is not None:
+            fr.pack_volumes(vols)
+        if imgs is not None:
+            fr.set_sources(pose_ref["w2cs"], pose_ref["intrinsics"])
+            if img_feat is None:
+                img_feat = torch.zeros((imgs.shape[1], 1, 8, H, W), device=imgs.device)
+            if confidence is None:
+                confidence = torch.zeros((1, H, W), device=imgs.device)
+            fr.pack_sources(imgs, img_feat, confidence)
+        else:
+            fr.c.V = 1
+            conf = confidence.to(torch.float32).reshape(H, W).contiguous()
+            fr._keep["conf"] = conf
+            fr.c.conf = conf.data_ptr()
+        _cache_put(key, fr)
+    return fr
+
+
+def gather_features(volume_feature, imgs, img_feat, confidence, pose_ref, rays_pts, rays_ndc, with_idx=False,
+                    parts=L.PART_ALL):
+    """Fused index_point_feature + build_color_volume (+ assembly, renderer.py:191-207) -> input_feat [R,S,F]."""
+    _need_cuda(rays_pts if rays_pts is not None else rays_ndc["stage1"], "gen_pts_feats")
+    fr = _maps_frame(volume_feature, imgs, img_feat, confidence, pose_ref)
+    if rays_pts is None:
+        rays_pts = rays_ndc["stage1"]
+    if rays_ndc is None:
+        rays_ndc = {k: rays_pts for k in ("stage1", "stage2", "stage3")}
+    R, S = rays_pts.shape[:2]
+    feat = torch.empty((R, S, fr.F), device=rays_pts.device)
+    idx = torch.empty((R, S, 11 + 3 * fr.c.V), device=rays_pts.device, dtype=torch.int32) if with_idx else None
+    args = [rays_pts, rays_ndc["stage1"], rays_ndc["stage2"], rays_ndc["stage3"]]
+    args = [a.to(torch.float32).contiguous() for a in args]
+    L.check(L.load().ucn_gather(C.byref(fr.c), *[L.ptr(a) for a in args], R * S, parts, L.ptr(feat), L.ptr(idx),
+                                L.stream_ptr()), "ucn_gather")
+    return (feat, idx) if with_idx else feat
+
+
+def index_point_feature(volume_feature, volume_confidence, ray_coordinate_ref, chunk=-1):
+    """utils/utils.py:833-893 -> (out_features [R,S,24], confidence_sampled [R,S])."""
+    feat = gather_features(volume_feature, None, None, volume_confidence, None, None, ray_coordinate_ref,
+                           parts=L.PART_VOLUMES)
+    return feat[..., :24], feat[..., -1]
+
+
+def build_color_volume(point_samples, pose_ref, imgs, near_far=None, img_feat=None, confidence=None, downscale=1.0,
+                       with_mask=False):
+    """utils/utils.py:742-799 -> colors [R,S,4V (+8V when img_feat is given)]."""
+    V = imgs.shape[1]
+    feat = gather_features(None, imgs, img_feat, None, pose_ref, point_samples, None, parts=L.PART_VIEWS)
+    return feat[..., 24:24 + (12 if img_feat is not None else 4) * V]
