@@ -110,6 +110,11 @@ extern "C" int ucn_pack_weights(const ucn_state_dict *sd, float *dst, void *dst_
     if (bias16) cudaMemcpyAsync(bias16 + off16, src, n * sizeof(float), cudaMemcpyDeviceToDevice, st);
   };
   const int NS = INT_MAX;
+  if (hb) {   // film / fb biases ride in the MMA: bias row at k = K_real of the bf16 tile (ones column in A)
+    pack_w_bf16_kernel<<<1, 128, 0, st>>>(sd->film_b, 128, 1, reinterpret_cast<__nv_bfloat16 *>(reinterpret_cast<char *>(hb) + B.film), 128, 0, 24 + 4 * V, NS);
+    pack_w_bf16_kernel<<<1, 128, 0, st>>>(sd->fb_b, 128, 1, reinterpret_cast<__nv_bfloat16 *>(reinterpret_cast<char *>(hb) + B.fb), 128, 0, 8 * V, NS);
+    ucn_count_launch(2);
+  }
   mat(sd->film_w, 128, 24 + 4 * V, L.film, 128, B.film, 128, 0, 0, NS);  vec(sd->film_b, 128, L.film_b, B.b_film);
   mat(sd->fb_w, 128, 8 * V, L.fb, 128, B.fb, 128, 0, 0, NS);              vec(sd->fb_b, 128, L.fb_b, B.b_fb);
   for (int i = 0; i < 6; ++i) {

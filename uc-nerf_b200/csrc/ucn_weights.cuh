@@ -46,8 +46,8 @@ struct BF16Layout {
   size_t film, fb, pts[6], feat, vv, base, adapt, bias, total_bytes;   // byte offsets
   size_t b_film, b_fb, b_pts[6], b_feat, b_vv, b_base, b_adapt;        // float offsets inside the bias block
   __host__ __device__ explicit BF16Layout(int V_) : V(V_) {
-    Kfilm = (24 + 4 * V_ + 15) & ~15;
-    Kfb = (8 * V_ + 15) & ~15;
+    Kfilm = (24 + 4 * V_ + 1 + 15) & ~15;    // +1: row k = 24+4V holds the bias (A operand carries a ones column)
+    Kfb = (8 * V_ + 1 + 15) & ~15;           // +1: row k = 8V holds the bias
     size_t o = 0;
     auto take = [&](size_t n_elems) { size_t r = o; o += (n_elems * 2 + 127) & ~size_t(127); return r; };
     film = take((size_t)128 * Kfilm);
