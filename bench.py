@@ -124,7 +124,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default=os.environ.get("UCNERF_BENCH_MODE", "bf16"), choices=["bf16", "fp32"])
+    ap.add_argument("--mode", default=os.environ.get("UCNERF_BENCH_MODE", "bf16"), choices=["bf16", "bf16_fast", "fp32"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--max-rays", type=int, default=0, help="rays per launch group (0 = auto)")
     ap.add_argument("--cpu-rays", type=int, default=8192, help="bounded CPU sample (rays) for the baseline")
@@ -250,7 +250,7 @@ def main():
         line = {
             "metric": "rays/sec", "value": world * n_rays / (ms * 1e-3), "unit": "rays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.mode == "bf16" else "f32",
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.mode == "fp32" else "bf16",
             "data": "synthetic",
             "config": {"workload": wl["name"], "H": H, "W": W, "source_views": V, "samples_per_ray": S,
                        "mlp_mode": args.mode, "rays_per_launch_group": max_rays,
@@ -261,7 +261,7 @@ def main():
                     "d2h_bytes_per_step": n_rays * 16, "ms_per_step": e2e_ms},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"kernel": "mlp_tc_kernel" if args.mode == "bf16" else "mlp_fp32_kernel", "bound": "tensor",
+            "roofline": {"kernel": {"bf16": "mlp_x3_kernel", "bf16_fast": "mlp_tc_kernel", "fp32": "mlp_fp32_kernel"}[args.mode], "bound": "tensor",
                          "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
                          "traffic": None, "peak_source": pk["_source"] + " (bf16_tflops_sustained)",
                          "flops_per_launch": flops_per_launch, "ms_per_launch": mlp_ms_per_launch},

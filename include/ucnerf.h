@@ -36,8 +36,13 @@ enum {
   UCN_E_WORKSPACE = -3     /* workspace too small (see ucn_frame_workspace_bytes)   */
 };
 
-/* MLP arithmetic. FP32 = SIMT fp32 (parity mode, 1e-4 gate); BF16_TC = tcgen05 bf16, fp32 accumulate. */
-enum { UCN_MLP_FP32 = 0, UCN_MLP_BF16_TC = 1 };
+/* MLP arithmetic.
+ *   FP32      SIMT fp32 (parity mode, 1e-4 gate).
+ *   BF16X3_TC tcgen05, split-bf16 operands (hi + lo, three MMAs per K step), fp32 accumulate in TMEM: the
+ *             production tensor-core path; meets the 1e-3 per-pixel RGB / 0.05 dB gate.
+ *   BF16_TC   tcgen05, single-pass bf16 operands: fastest, but plain bf16 rounding of a 6-layer FiLM MLP
+ *             gives ~2e-2 worst-case RGB error on random-init weights, so it is opt-in only. */
+enum { UCN_MLP_FP32 = 0, UCN_MLP_BF16_TC = 1, UCN_MLP_BF16X3_TC = 2 };
 
 /* One target view ("frame"): cameras by value, packed maps by device pointer.
  * Packed layouts (produced by ucn_pack_*):
@@ -72,6 +77,7 @@ typedef struct ucn_weights {
   int32_t reserved;
   const float *f32;         /* fp32 pack: transposed [K][N] matrices + biases  */
   const void *bf16;         /* bf16 pack: UMMA K-major core-matrix tiles (may be NULL if unused) */
+  const void *bf16x3;       /* split-bf16 (hi/lo) pack for UCN_MLP_BF16X3_TC (may be NULL if unused) */
 } ucn_weights;
 
 /* Pointers to the reference state_dict tensors (torch layout [out,in], fp32, DEVICE memory).
@@ -107,7 +113,9 @@ int ucn_pack_channels_last(const float *src, float *dst, int B, int Cn, int64_t 
 int ucn_pack_nearfar(const float *depth_values, float *dst, int D, int h, int w, void *stream);
 size_t ucn_weights_f32_bytes(int V);
 size_t ucn_weights_bf16_bytes(int V);
-int ucn_pack_weights(const ucn_state_dict *sd, float *dst_f32, void *dst_bf16, void *stream);
+size_t ucn_weights_bf16x3_bytes(int V);
+/* any destination may be NULL (that pack is skipped) */
+int ucn_pack_weights(const ucn_state_dict *sd, float *dst_f32, void *dst_bf16, void *dst_bf16x3, void *stream);
 
 /* ---- K1: ray generation + depth-bounded sampling (+ target-view NDC) -------------------------
  * replaces get_rays_mvs (utils/utils.py:217-271, eval branch and explicit-pixel branch),

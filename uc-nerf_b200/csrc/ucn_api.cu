@@ -25,6 +25,9 @@ int ucn_mlp_forward_fp32(const ucn_weights *w, const float *ndc_pts, const float
                          int S, float *raw, void *stream);
 int ucn_mlp_forward_tc(const ucn_weights *w, const float *ndc_pts, const float *feat, const float *angle, int R,
                        int S, float *raw, void *stream);
+int ucn_mlp_forward_x3(const ucn_weights *w, const float *ndc_pts, const float *feat, long long f_tile_stride,
+                       long long f_k_stride, long long f_row_stride, const float *angle, int R, int S, float *raw,
+                       void *stream);
 
 extern "C" int ucn_version(void) { return 100; }
 extern "C" const char *ucn_last_error(void) { return g_err; }
@@ -53,6 +56,10 @@ extern "C" int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const
   if (R <= 0) return UCN_OK;
   if (mode == UCN_MLP_FP32) return ucn_mlp_forward_fp32(w, ndc_pts, feat, angle, R, S, raw, stream);
   if (mode == UCN_MLP_BF16_TC) return ucn_mlp_forward_tc(w, ndc_pts, feat, angle, R, S, raw, stream);
+  if (mode == UCN_MLP_BF16X3_TC) {
+    const long long F = 24 + 12 * w->V + 1;                       // row-major [N][F] rows (the reference layout)
+    return ucn_mlp_forward_x3(w, ndc_pts, feat, 128 * F, 1, F, angle, R, S, raw, stream);
+  }
   return ucn_set_error(UCN_E_ARG, "ucn_mlp_forward: unknown mode");
 }
 

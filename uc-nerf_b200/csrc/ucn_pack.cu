@@ -62,6 +62,29 @@ __global__ void pack_w_bf16_kernel(const float *__restrict__ src, int Nout, int 
   dst[((size_t)(k >> 3) * Ntile + n) * 8 + (k & 7)] = __float2bfloat16_rn(src[i]);
 }
 
+__global__ void pack_vd_kernel(const float *__restrict__ src, float *__restrict__ vd, int n_off) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;          // src [64][155]
+  if (i >= 64 * 27) return;
+  const int n = i / 27, k = i % 27;
+  vd[k * 128 + n_off + n] = src[n * 155 + 128 + k];
+}
+
+// split-bf16 unit layout (ucn::X3Layout): element (n,k) -> unit k/16: hi tile, then lo tile at +4096 B
+__global__ void pack_w_x3_kernel(const float *__restrict__ src, int Nout, int K, int k_src0, int k_cnt,
+                                 unsigned char *__restrict__ dst, int n_off, int k_off) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Nout * k_cnt) return;
+  const int n = i / k_cnt + n_off, ks = i % k_cnt;
+  const float w = src[(size_t)(i / k_cnt) * K + k_src0 + ks];
+  const int k = ks + k_off, u = k >> 4, kk = k & 15;
+  const __nv_bfloat16 hi = __float2bfloat16_rn(w);
+  const __nv_bfloat16 lo = __float2bfloat16_rn(w - __bfloat162float(hi));
+  __nv_bfloat16 *t = reinterpret_cast<__nv_bfloat16 *>(dst + (size_t)u * ucn::X3Layout::kUnit);
+  const int e = ((kk >> 3) * 128 + n) * 8 + (kk & 7);
+  t[e] = hi;
+  t[2048 + e] = lo;
+}
+
 }  // namespace
 
 extern "C" int ucn_pack_channels_last(const float *src, float *dst, int B, int Cn, int64_t N, int Cpad, void *stream) {
@@ -81,9 +104,57 @@ extern "C" int ucn_pack_nearfar(const float *depth_values, float *dst, int D, in
 
 extern "C" size_t ucn_weights_f32_bytes(int V) { return ucn::F32Layout(V).total * sizeof(float); }
 extern "C" size_t ucn_weights_bf16_bytes(int V) { return ucn::BF16Layout(V).total_bytes; }
+extern "C" size_t ucn_weights_bf16x3_bytes(int V) { return ucn::X3Layout(V).total_bytes; }
 
-extern "C" int ucn_pack_weights(const ucn_state_dict *sd, float *dst, void *dst_bf16, void *stream_) {
-  UCN_CHECK_ARG(sd && (dst || dst_bf16), "ucn_pack_weights: null argument");
+static int pack_weights_x3(const ucn_state_dict *sd, unsigned char *dst, cudaStream_t st) {
+  const int V = sd->V;
+  const ucn::X3Layout X(V);
+  cudaError_t e = cudaMemsetAsync(dst, 0, X.total_bytes, st);
+  if (e != cudaSuccess) return ucn_cuda_status(e, "memset x3 pack");
+  auto mat = [&](const float *src, int Nout, int K, int k_src0, int k_cnt, size_t off, int n_off, int k_off) {
+    const int n = Nout * k_cnt;
+    pack_w_x3_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, Nout, K, k_src0, k_cnt, dst + off, n_off, k_off);
+    ucn_count_launch();
+  };
+  float *f32 = reinterpret_cast<float *>(dst + X.f32);
+  auto vec = [&](const float *src, int n, int off) {
+    cudaMemcpyAsync(f32 + off, src, n * sizeof(float), cudaMemcpyDeviceToDevice, st);
+  };
+  const int Kf = 24 + 4 * V, Kb = 8 * V;
+  mat(sd->film_w, 128, Kf, 0, Kf, X.film, 0, 0);
+  mat(sd->film_b, 128, 1, 0, 1, X.film, 0, Kf);                  // bias row (A carries a ones column at k = Kf)
+  mat(sd->fb_w, 128, Kb, 0, Kb, X.fb, 0, 0);
+  mat(sd->fb_b, 128, 1, 0, 1, X.fb, 0, Kb);
+  mat(sd->pts_w[0], 128, 63, 0, 63, X.pts0, 0, 0);
+  for (int i = 1; i < 5; ++i) mat(sd->pts_w[i], 128, 128, 0, 128, X.pts14[i - 1], 0, 0);
+  mat(sd->pts_w[5], 128, 191, 63, 128, X.pts5h, 0, 0);           // skip layer: input = [PE63 | h]  (models.py:156)
+  mat(sd->pts_w[5], 128, 191, 0, 63, X.pts5pe, 0, 0);
+  mat(sd->feature_w, 128, 128, 0, 128, X.feat, 0, 0);
+  mat(sd->views_w, 64, 155, 0, 128, X.vvh, 0, 0);
+  mat(sd->vconf_w, 64, 155, 0, 128, X.vvh, 64, 0);
+  for (int i = 0; i < 6; ++i) vec(sd->pts_b[i], 128, X.b_pts + 128 * i);
+  vec(sd->feature_b, 128, X.b_feat);
+  vec(sd->views_b, 64, X.b_vv);
+  vec(sd->vconf_b, 64, X.b_vv + 64);
+  // heads and view-direction rows stay fp32 (CUDA-core epilogues): w_base [k][4], w_adapt [k][4], vd [k][128]
+  pack_w_f32_kernel<<<2, 256, 0, st>>>(sd->crgb_w, 3, 128, f32 + X.w_base, 4, 0, 0, INT_MAX);
+  pack_w_f32_kernel<<<1, 256, 0, st>>>(sd->alpha1_w, 1, 128, f32 + X.w_base, 4, 3, 0, INT_MAX);
+  pack_w_f32_kernel<<<1, 256, 0, st>>>(sd->rgb_w, 3, 64, f32 + X.w_adapt, 4, 0, 0, INT_MAX);
+  pack_w_f32_kernel<<<1, 256, 0, st>>>(sd->alpha_w, 1, 64, f32 + X.w_adapt, 4, 3, 64, INT_MAX);
+  ucn_count_launch(4);
+  vec(sd->crgb_b, 3, X.b_base); vec(sd->alpha1_b, 1, X.b_base + 3);
+  vec(sd->rgb_b, 3, X.b_adapt); vec(sd->alpha_b, 1, X.b_adapt + 3);
+  // vd[k][n] = W[n][128 + k]: rows 128..154 of the K dimension of views_linears.0 / view_confi_linears.0
+  pack_vd_kernel<<<(27 * 64 + 255) / 256, 256, 0, st>>>(sd->views_w, f32 + X.vd, 0);
+  pack_vd_kernel<<<(27 * 64 + 255) / 256, 256, 0, st>>>(sd->vconf_w, f32 + X.vd, 64);
+  ucn_count_launch(2);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_pack_weights(x3)");
+  return UCN_OK;
+}
+
+extern "C" int ucn_pack_weights(const ucn_state_dict *sd, float *dst, void *dst_bf16, void *dst_x3, void *stream_) {
+  UCN_CHECK_ARG(sd && (dst || dst_bf16 || dst_x3), "ucn_pack_weights: null argument");
   UCN_CHECK_ARG(sd->V >= 1 && sd->V <= UCN_MAX_V, "ucn_pack_weights: 1 <= V <= 8");
   cudaStream_t st = (cudaStream_t)stream_;
   const int V = sd->V;
@@ -131,5 +202,6 @@ extern "C" int ucn_pack_weights(const ucn_state_dict *sd, float *dst, void *dst_
   mat(sd->alpha_w, 1, 64, L.adapt, 4, B.adapt, 16, 3, 64, NS);            vec(sd->alpha_b, 1, L.adapt_b + 3, B.b_adapt + 3);
   e = cudaGetLastError();
   if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_pack_weights");
+  if (dst_x3) return pack_weights_x3(sd, reinterpret_cast<unsigned char *>(dst_x3), st);
   return UCN_OK;
 }

@@ -68,4 +68,37 @@ struct BF16Layout {
   }
 };
 
+
+// split-bf16 pack (tcgen05 "x3" mode, the parity-grade tensor-core path): every weight w is stored as
+// hi = bf16(w) and lo = bf16(w - hi); the kernel issues A_hi*W_hi + A_lo*W_hi + A_hi*W_lo per K step,
+// which carries ~16 significant bits per operand with fp32 accumulation.  A matrix [128][K] (K padded to
+// 16) is a sequence of K/16 "units"; unit u = [hi tile 4096 B][lo tile 4096 B], each tile the UMMA
+// no-swizzle K-major core-matrix layout of a 128 x 16 block: element (n,kk) at ((kk/8)*128 + n)*8 + kk%8.
+//   film [Kfilm]  (row k = 24+4V carries the bias: the A operand has a ones column there)
+//   pts0 [64]  pts1..4 [128]  pts5h [128] (skip layer, hidden part)  pts5pe [64] (skip layer, PE part)
+//   fb [Kfb] (bias row at k = 8V)   feat [128]   vvh [128] (views|view_confi on the feature part)
+// followed by an fp32 block: b_pts[6*128] b_feat[128] b_vv[128] w_base[128][4] w_adapt[128][4] b_base[4]
+// b_adapt[4] (kSmemFloats floats, copied to shared memory) and vd[28][128] (view-direction rows of
+// views|view_confi, applied per ray on the CUDA cores).
+struct X3Layout {
+  static constexpr int kUnit = 8192;
+  static constexpr int kSmemFloats = 6 * 128 + 128 + 128 + 512 + 512 + 4 + 4;
+  int V, Kfilm, Kfb;
+  size_t film, pts0, pts14[4], pts5h, pts5pe, fb, feat, vvh, f32, total_bytes;   // byte offsets
+  // float offsets inside the fp32 block
+  static constexpr int b_pts = 0, b_feat = 768, b_vv = 896, w_base = 1024, w_adapt = 1536, b_base = 2048,
+                       b_adapt = 2052, vd = 2056;
+  __host__ __device__ explicit X3Layout(int V_) : V(V_) {
+    Kfilm = (24 + 4 * V_ + 1 + 15) & ~15;
+    Kfb = (8 * V_ + 1 + 15) & ~15;
+    size_t o = 0;
+    auto take = [&](int K) { size_t r = o; o += (size_t)(K / 16) * kUnit; return r; };
+    film = take(Kfilm); pts0 = take(64);
+    for (int i = 0; i < 4; ++i) pts14[i] = take(128);
+    pts5h = take(128); pts5pe = take(64); fb = take(Kfb); feat = take(128); vvh = take(128);
+    f32 = o;
+    total_bytes = o + (size_t)(vd + 28 * 128) * sizeof(float);
+  }
+};
+
 }  // namespace ucn

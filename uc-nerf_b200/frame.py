@@ -193,10 +193,12 @@ class PackedWeights:
             setattr(c, field + "_b", sd[f"nerf.{name}.bias"].data_ptr())
         self.f32 = torch.empty(lib.ucn_weights_f32_bytes(V) // 4, device=self.device, dtype=torch.float32)
         self.bf16 = torch.empty(lib.ucn_weights_bf16_bytes(V), device=self.device, dtype=torch.uint8)
-        L.check(lib.ucn_pack_weights(C.byref(c), L.ptr(self.f32), L.ptr(self.bf16), L.stream_ptr()), "ucn_pack_weights")
+        self.bf16x3 = torch.empty(lib.ucn_weights_bf16x3_bytes(V), device=self.device, dtype=torch.uint8)
+        L.check(lib.ucn_pack_weights(C.byref(c), L.ptr(self.f32), L.ptr(self.bf16), L.ptr(self.bf16x3), L.stream_ptr()),
+                "ucn_pack_weights")
         torch.cuda.current_stream().synchronize()      # sd temporaries may be freed after this
         self.c = L.Weights()
-        self.c.V, self.c.f32, self.c.bf16 = V, self.f32.data_ptr(), self.bf16.data_ptr()
+        self.c.V, self.c.f32, self.c.bf16, self.c.bf16x3 = V, self.f32.data_ptr(), self.bf16.data_ptr(), self.bf16x3.data_ptr()
         self.V = V
 
 

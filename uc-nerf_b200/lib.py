@@ -9,9 +9,11 @@ LIB_PATH = os.path.join(_HERE, "libucnerf.so")
 
 UCN_MAX_V = 8
 UCN_MAX_S = 1024
-MLP_FP32, MLP_BF16_TC = 0, 1
+MLP_FP32, MLP_BF16_TC, MLP_BF16X3_TC = 0, 1, 2
 PART_VOLUMES, PART_VIEWS, PART_ALL = 1, 2, 3
-MODES = {"fp32": MLP_FP32, "bf16": MLP_BF16_TC}
+# "bf16" is the production tensor-core mode: split-bf16 operands (meets the 1e-3 RGB gate);
+# "bf16_fast" is single-pass bf16 (about 2e-2 worst-case RGB error on random-init weights), opt-in only.
+MODES = {"fp32": MLP_FP32, "bf16": MLP_BF16X3_TC, "bf16_fast": MLP_BF16_TC}
 
 _fp = C.c_void_p
 
@@ -28,7 +30,7 @@ class Frame(C.Structure):
 
 
 class Weights(C.Structure):
-    _fields_ = [("V", C.c_int32), ("reserved", C.c_int32), ("f32", _fp), ("bf16", _fp)]
+    _fields_ = [("V", C.c_int32), ("reserved", C.c_int32), ("f32", _fp), ("bf16", _fp), ("bf16x3", _fp)]
 
 
 class StateDict(C.Structure):
@@ -52,7 +54,8 @@ _SIGS = {
     "ucn_pack_nearfar": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp]),
     "ucn_weights_f32_bytes": (C.c_size_t, [C.c_int]),
     "ucn_weights_bf16_bytes": (C.c_size_t, [C.c_int]),
-    "ucn_pack_weights": (C.c_int, [C.POINTER(StateDict), _fp, _fp, _fp]),
+    "ucn_weights_bf16x3_bytes": (C.c_size_t, [C.c_int]),
+    "ucn_pack_weights": (C.c_int, [C.POINTER(StateDict), _fp, _fp, _fp, _fp]),
     "ucn_raygen_sample": (C.c_int, [C.POINTER(Frame), _fp, C.c_int, C.c_int, _fp, _fp, C.c_uint64, _fp, _fp, _fp,
                                     _fp, _fp]),
     "ucn_gather": (C.c_int, [C.POINTER(Frame), _fp, _fp, _fp, _fp, C.c_int64, C.c_int, _fp, _fp, _fp]),
