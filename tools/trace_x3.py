@@ -1,0 +1,42 @@
+"""Timeline of CTA 0 of mlp_x3_kernel (debug): per-round MMA-issue and epilogue intervals in cycles."""
+import ctypes as C, sys, os
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), ".."))
+import numpy as np, torch
+from ucnerf_b200 import lib as L, synthetic
+from ucnerf_b200.frame import PackedWeights
+lib = L.load()
+lib.ucn_debug_set_trace.argtypes = [C.c_void_p]
+V, S, R = 3, 126, 148 * 2 * 128 * 6 // 126
+F = 24 + 12 * V + 1
+pw = PackedWeights(synthetic.make_weights(V, seed=0), V, "cuda")
+g = torch.Generator("cuda").manual_seed(0)
+ndc = torch.rand((R * S, 3), device="cuda", generator=g)
+feat = torch.randn((R * S, F), device="cuda", generator=g)
+feat[:, -1] = torch.rand(R * S, device="cuda", generator=g)
+ang = torch.randn((R, 3), device="cuda", generator=g)
+raw = torch.empty((R * S, 4), device="cuda")
+CAP = 2048
+buf = torch.zeros(7 * CAP * 2, dtype=torch.int64, device="cuda")
+def run():
+    L.check(lib.ucn_mlp_forward(C.byref(pw.c), L.ptr(ndc), L.ptr(feat), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
+flags = int(os.environ.get("X3_DBG", "0"))
+L.check(lib.ucn_debug_set_flags(flags), "flags")
+run(); torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(); run(); e1.record(); torch.cuda.synchronize()
+print(f"flags {flags}: kernel {e0.elapsed_time(e1):.3f} ms for {R * S} samples -> {R * S / e0.elapsed_time(e1) / 1e3:.1f} Msamples/s")
+L.check(lib.ucn_debug_set_trace(C.c_void_p(buf.data_ptr())), "trace")
+run(); torch.cuda.synchronize()
+L.check(lib.ucn_debug_set_trace(None), "trace")
+b = buf.cpu().numpy().reshape(7, CAP, 2)
+ev = []
+for who in range(7):
+    for w, t in b[who]:
+        if t: ev.append((int(t), int(w) & 0xFF, (int(w) >> 8) & 0xFF, (int(w) >> 16) & 0xFF, int(w) >> 24))
+ev.sort(); t0 = ev[0][0]
+names = {1: "mma_start", 2: "mma_issued", 3: "epi_wake", 4: "epi_done", 5: "blk_issued"}
+lo, hi = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (0, 200)
+for t, tag, r, who, pay in ev[lo:hi]:
+    extra = f"  wfull_wait={pay}" if tag == 2 else ""
+    print(f"{t - t0:>8} {names[tag]:<11} r{r} {'wg' if tag in (3, 4) else 'slot'}{who}{extra}")
+print("events", len(ev), "span cycles", ev[-1][0] - t0)

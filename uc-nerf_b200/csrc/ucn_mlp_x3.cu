@@ -54,6 +54,25 @@ constexpr uint32_t STAGE = 2 * ucn::X3Layout::kUnit;   // 16 KB ring stage = two
 constexpr int NROUND = 10;
 constexpr int MAXBLK = 48;
 
+// optional timeline trace of CTA 0 (debug aid for profiling the round pipeline; off unless a buffer is set).
+// Each tracer (0 = MMA thread, 1..4 = warpgroup leaders, 5 = producer) owns a private region: no atomics.
+__device__ long long *g_trace = nullptr;
+__device__ int g_dbg = 0;      // experiment switches for tools/trace_x3.py (timing experiments only; results may be wrong)
+constexpr int kTraceCap = 2048;
+struct Tracer {
+  long long *base; int n;
+  __device__ __forceinline__ Tracer(int who) : base(nullptr), n(0) {
+    if (g_trace && blockIdx.x == 0) base = g_trace + (size_t)who * kTraceCap * 2;
+  }
+  __device__ __forceinline__ void ev(int tag, int r, int who, long long payload = 0) {
+    if (base && n < kTraceCap) {
+      base[2 * n] = (long long)tag | ((long long)r << 8) | ((long long)who << 16) | (payload << 24);
+      base[2 * n + 1] = clock64();
+      ++n;
+    }
+  }
+};
+
 enum { BF_FRESH = 1, BF_MOD = 2, BF_TS = 4 };
 struct Blk { uint32_t goff; uint8_t units, a0, flags, pad; };   // a0: first A K-chunk (SS) / first K16 unit (TS)
 struct Plan {
@@ -164,19 +183,27 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
   extern __shared__ __align__(1024) unsigned char smem[];
   const ucn::X3Layout L(V);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nst = plan.nst, rpt = plan.rpt;
+  const int nst = plan.nst, rpt = plan.rpt, nblk = plan.nblk;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t ring = sbase + 2 * SLOT;
-  const uint32_t bar_in = sbase + plan.off_bars, bar_acc = bar_in + 16, bar_wfull = bar_in + 32,
-                 bar_wempty = bar_wfull + 8 * nst, tmem_ptr_addr = bar_wempty + 8 * nst;
+  const uint32_t bar_in = pin(sbase + plan.off_bars), bar_acc = pin(bar_in + 16), bar_wfull = pin(bar_in + 32),
+                 bar_wempty = pin(bar_wfull + 8 * nst), tmem_ptr_addr = bar_wempty + 8 * nst;
   float *f32s = reinterpret_cast<float *>(smem + plan.off_f32);
   float4 *exch_s = reinterpret_cast<float4 *>(smem + plan.off_exch);
   float *rayb_s = reinterpret_cast<float *>(smem + plan.off_rayb);
+  __shared__ uint32_t blk_s[MAXBLK], goff_s[MAXBLK];
+  __shared__ int rb_s[NROUND + 1];
   const int F = 24 + 12 * V + 1, Kfilm_real = 24 + 4 * V, Kfb_real = 8 * V;
   const float *f32g = reinterpret_cast<const float *>(wpack + L.f32);
 
   // ---- one-time setup ---------------------------------------------------------------------------
   for (int i = threadIdx.x; i < ucn::X3Layout::kSmemFloats; i += kThreads) f32s[i] = f32g[i];
+  if (threadIdx.x < plan.nblk) {
+    const Blk k = plan.blk[threadIdx.x];
+    blk_s[threadIdx.x] = (uint32_t)k.units | ((uint32_t)k.a0 << 8) | ((uint32_t)k.flags << 16);
+    goff_s[threadIdx.x] = k.goff;
+  }
+  if (threadIdx.x <= NROUND) rb_s[threadIdx.x] = plan.round_begin[threadIdx.x];
   if (threadIdx.x == 0) {
     mbar_init(bar_in, 8); mbar_init(bar_in + 8, 8);
     mbar_init(bar_acc, 1); mbar_init(bar_acc + 8, 1);
@@ -195,60 +222,91 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
   if (warp == 0) {
     // ================= weight producer ===========================================================
     if (lane == 0) {
-      uint32_t cnt = 0;
+      // A round's weight blocks are loaded once per tile pair and used by both slots (slot 1 runs about half a
+      // period behind slot 0); a stage is released when the last slot's MMAs on it have completed.
+      uint32_t st = 0, wph = 1;
       for (long long p = blockIdx.x; p < npairs; p += gridDim.x) {
-        for (int b = 0; b < plan.nblk; ++b, ++cnt) {
-          const uint32_t st = cnt % nst, ph = (cnt / nst) & 1;
-          const uint32_t bytes = (uint32_t)plan.blk[b].units * ucn::X3Layout::kUnit;
-          mbar_wait(bar_wempty + 8 * st, ph ^ 1);
+#pragma unroll 1
+        for (int b = 0; b < nblk; ++b) {
+          const uint32_t bytes = (blk_s[b] & 0xFF) * ucn::X3Layout::kUnit;
+          mbar_wait(bar_wempty + 8 * st, wph);
           mbar_expect_tx(bar_wfull + 8 * st, bytes);
-          bulk_g2s(ring + st * STAGE, wpack + plan.blk[b].goff, bytes, bar_wfull + 8 * st);
+          bulk_g2s(ring + st * STAGE, wpack + goff_s[b], bytes, bar_wfull + 8 * st);
+          if (++st == (uint32_t)nst) { st = 0; wph ^= 1; }
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // ================= MMA issuer =================================================================
-    if (lane == 0) {
+    // The whole warp runs this loop convergently (one elected lane issues each MMA), kept to a handful of
+    // integer instructions per MMA:
+    // every descriptor is "template + (address >> 4)" (LBO/SBO/version bits never change), the ring stage and
+    // its phase are running counters, and the block table is read from shared memory.
+    {
       const uint32_t idesc = umma_idesc_bf16(128);
-      uint32_t cnt = 0, ph_in[2] = {0, 0};
+      const uint64_t dt = umma_desc(0, CHUNK, 128);               // LBO = 2048 (A chunks and B tiles alike), SBO = 128
+      const uint32_t dhi = (uint32_t)(dt >> 32), dlo = (uint32_t)dt;
+      auto mk = [&](uint32_t lo) { return ((uint64_t)dhi << 32) | lo; };
+      uint32_t st0 = 0, wph0 = 0, ph_in0 = 0, ph_in1 = 0;      // ring position of the current round's first block
+      Tracer tr(0);
+      if (lane != 0) tr.base = nullptr;
+      const uint32_t ring_lo = dlo + (ring >> 4);
       for (long long p = blockIdx.x; p < npairs; p += gridDim.x) {
         const int nslots = (2 * p + 1 < ntiles) ? 2 : 1;
+#pragma unroll 1
         for (int r = 0; r < NROUND; ++r) {
-          const int b0 = plan.round_begin[r], b1 = plan.round_begin[r + 1];
+          const int b0 = rb_s[r], b1 = rb_s[r + 1];
+#pragma unroll 1
           for (int s = 0; s < nslots; ++s) {
-            mbar_wait(bar_in + 8 * s, ph_in[s]);
-            ph_in[s] ^= 1;
+            if (s == 0) { mbar_wait(bar_in, ph_in0); ph_in0 ^= 1; } else { mbar_wait(bar_in + 8, ph_in1); ph_in1 ^= 1; }
             tc_fence_after();
-            const uint32_t slot_addr = sbase + s * SLOT;
+            tr.ev(1, r, s);
+            long long wwait = 0;
+            const uint32_t a_lo = dlo + ((sbase + s * SLOT) >> 4);
+            const uint32_t t_slot = tmem_base + s * 256;
+            uint32_t st = st0, wph = wph0;
+#pragma unroll 1
             for (int b = b0; b < b1; ++b) {
-              const Blk k = plan.blk[b];
-              const uint32_t c = cnt + (b - b0), st = c % nst;
-              if (s == 0) { mbar_wait(bar_wfull + 8 * st, (c / nst) & 1); tc_fence_after(); }
-              const uint32_t w_addr = ring + st * STAGE;
-              const uint32_t d = tmem_base + s * 256 + ((k.flags & BF_MOD) ? 0 : 128);
-              for (int u = 0; u < k.units; ++u) {
-                const uint64_t bh = umma_desc(w_addr + u * ucn::X3Layout::kUnit, 2048, 128);
-                const uint64_t bl = umma_desc(w_addr + u * ucn::X3Layout::kUnit + 4096, 2048, 128);
-                const uint32_t first = ((k.flags & BF_FRESH) && u == 0) ? 0u : 1u;
-                if (k.flags & BF_TS) {
-                  const uint32_t ah = tmem_base + s * 256 + 128 + 64 + 8 * (k.a0 + u), al = ah + 32;
-                  umma_ts(d, ah, bh, idesc, first);
-                  umma_ts(d, al, bh, idesc, 1u);
-                  umma_ts(d, ah, bl, idesc, 1u);
-                } else {
-                  const uint64_t ah = umma_desc(slot_addr + (k.a0 + 2 * u) * CHUNK, CHUNK, 128);
-                  const uint64_t al = umma_desc(slot_addr + HALF + (k.a0 + 2 * u) * CHUNK, CHUNK, 128);
-                  umma_ss(d, ah, bh, idesc, first);
-                  umma_ss(d, al, bh, idesc, 1u);
-                  umma_ss(d, ah, bl, idesc, 1u);
+              const uint32_t info = blk_s[b];                     // units | a0 << 8 | flags << 16
+              const uint32_t units = info & 0xFF, a0 = (info >> 8) & 0xFF, flags = info >> 16;
+              const long long w0 = tr.base ? clock64() : 0;
+              if (s == 0) mbar_wait(bar_wfull + 8 * st, wph);       // slot 1 reuses the stage slot 0 waited for
+              if (tr.base) wwait += clock64() - w0;
+              // (no tcgen05 fence here: the stage was filled by the bulk-copy engine, not by tcgen05 ops, and a
+              //  fence per block stalls the MMA pipeline -- measured 91 vs 67 cycles per MMA)
+              const uint32_t b_lo = ring_lo + st * (STAGE >> 4);
+              const uint32_t d = t_slot + ((flags & BF_MOD) ? 0 : 128);
+              const uint32_t first = (flags & BF_FRESH) ? 0u : 1u;
+              if (flags & BF_TS) {
+                const uint32_t ah = t_slot + 128 + 64 + 8 * a0;
+                umma_ts_w(d, ah, mk(b_lo), idesc, first);
+                umma_ts_w(d, ah + 32, mk(b_lo), idesc, 1u);
+                umma_ts_w(d, ah, mk(b_lo + 256), idesc, 1u);
+                if (units > 1) {
+                  umma_ts_w(d, ah + 8, mk(b_lo + 512), idesc, 1u);
+                  umma_ts_w(d, ah + 40, mk(b_lo + 512), idesc, 1u);
+                  umma_ts_w(d, ah + 8, mk(b_lo + 768), idesc, 1u);
+                }
+              } else {
+                const uint32_t ah = a_lo + a0 * (CHUNK >> 4);       // lo part: + HALF >> 4
+                umma_ss_w(d, mk(ah), mk(b_lo), idesc, first);
+                umma_ss_w(d, mk(ah + (HALF >> 4)), mk(b_lo), idesc, 1u);
+                umma_ss_w(d, mk(ah), mk(b_lo + 256), idesc, 1u);
+                if (units > 1) {
+                  umma_ss_w(d, mk(ah + 256), mk(b_lo + 512), idesc, 1u);
+                  umma_ss_w(d, mk(ah + 256 + (HALF >> 4)), mk(b_lo + 512), idesc, 1u);
+                  umma_ss_w(d, mk(ah + 256), mk(b_lo + 768), idesc, 1u);
                 }
               }
-              if (s == nslots - 1) umma_commit(bar_wempty + 8 * st);   // stage free once both slots consumed it
+              tr.ev(5, r, s);
+              if (s == nslots - 1) umma_commit_w(bar_wempty + 8 * st);   // free once the last slot's MMAs have read it
+              if (++st == (uint32_t)nst) { st = 0; wph ^= 1; }
             }
-            umma_commit(bar_acc + 8 * s);
+            umma_commit_w(bar_acc + 8 * s);
+            if (s == nslots - 1) { st0 = st; wph0 = wph; }
+            tr.ev(2, r, s, wwait);
           }
-          cnt += b1 - b0;
         }
       }
     }
@@ -261,14 +319,18 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
     const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) << 5) << 16) + s * 256;
     const uint32_t t_mod = t_lane, t_acc = t_lane + 128;
     const int col0 = 64 * hf, bar_id = 1 + s;
+    const uint32_t my_acc = pin(bar_acc + 8 * s), my_in = pin(bar_in + 8 * s);
     const float *bias_s = f32s + ucn::X3Layout::b_pts;
     uint32_t ph_acc = 0;
+    Tracer tr(((warp & 3) == 0 && lane == 0) ? 1 + g : 6);
+    if (!((warp & 3) == 0 && lane == 0)) tr.base = nullptr;
     float head[4], base4[4] = {0.f, 0.f, 0.f, 0.f}, x[3] = {0.f, 0.f, 0.f}, u = 0.f;
+    const int dbg = g_dbg;
     auto arrive_in = [&]() {
       tc_fence_before();
-      fence_async_smem();
+      if (!(dbg & 1)) fence_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_in + 8 * s);
+      if (lane == 0) mbar_arrive(my_in);
     };
     for (long long p = blockIdx.x; p < npairs; p += gridDim.x) {
       const long long tile = 2 * p + s;
@@ -305,10 +367,13 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
 
 #pragma unroll 1
       for (int r = 0; r < NROUND; ++r) {
-        mbar_wait(bar_acc + 8 * s, ph_acc);
+        mbar_wait_backoff(my_acc, ph_acc);
         ph_acc ^= 1;
         tc_fence_after();
-        if (r < 5) {
+        tr.ev(3, r, g);
+        if (dbg & 2) {
+          // experiment: no epilogue work at all
+        } else if (r < 5) {
           epi64<0, false>(t_acc, t_mod, col0, bias_s + 128 * r, nullptr, h_row, nullptr, head);
         } else if (r == 5) {
           if (hf == 0) {                                         // skip connection: PE back into H[0..7]
@@ -384,6 +449,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
             if (valid) reinterpret_cast<float4 *>(raw)[q] = out;
           }
         }
+        tr.ev(4, r, g);
         if (r < NROUND - 1) arrive_in();
       }
     }
@@ -436,9 +502,18 @@ static int make_plan(int V, int S, Plan &P) {
     P.off_bars = o; o += (4 + 2 * nst) * 8 + 16;
     P.smem_total = o;
     P.nst = (uint8_t)nst;
-    if (o <= 232448u) return 0;
+    if (o <= 232448u - 1024u) return 0;              // 1 KB of static shared memory (block tables)
   }
   return -2;
+}
+
+extern "C" int ucn_debug_set_flags(int flags) {
+  cudaError_t e = cudaMemcpyToSymbol(g_dbg, &flags, sizeof(flags));
+  return e == cudaSuccess ? UCN_OK : ucn_cuda_status(e, "ucn_debug_set_flags");
+}
+extern "C" int ucn_debug_set_trace(long long *buf) {
+  cudaError_t e = cudaMemcpyToSymbol(g_trace, &buf, sizeof(buf));
+  return e == cudaSuccess ? UCN_OK : ucn_cuda_status(e, "ucn_debug_set_trace");
 }
 
 int ucn_mlp_forward_x3(const ucn_weights *w, const float *ndc_pts, const float *feat, long long f_tile_stride,
@@ -453,9 +528,9 @@ int ucn_mlp_forward_x3(const ucn_weights *w, const float *ndc_pts, const float *
   const long long N = (long long)R * S;
   static int attr_bytes = 0;
   if (attr_bytes < (int)P.smem_total) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+    cudaError_t e = cudaFuncSetAttribute(mlp_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.smem_total);
     if (e != cudaSuccess) return ucn_cuda_status(e, "mlp_x3 smem attribute");
-    attr_bytes = 232448;
+    attr_bytes = (int)P.smem_total;
   }
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
