@@ -149,6 +149,12 @@ int ucn_project_points(const float *w2c_host16, const float *K_host9, int H, int
 int ucn_gather_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R, float *feat,
                       float *ndc_pts, void *stream);
 
+/* same gathers, feature rows written in the tile-transposed interchange layout of the tensor-core MLP:
+ * feat_tiles [ceil(R*S/128)][F][128] (tile t, channel c, row r = sample 128 t + r; rows past R*S are zero).
+ * Both K2's stores and K3's per-row loads are then one coalesced 128-byte line per warp and channel. */
+int ucn_gather_tiles_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R,
+                            float *feat_tiles, float *ndc_pts, void *stream);
+
 /* view-direction feature: gen_dir_feature + prologue of rendering (network/renderer.py:163-174,232-239) */
 int ucn_dir_feature(const ucn_frame *f, const float *rays_d, int R, int ray_offset, float *angle, void *stream);
 
@@ -158,6 +164,10 @@ int ucn_dir_feature(const ucn_frame *f, const float *rays_d, int R, int ray_offs
  * ndc_pts [N][3], feat [N][F], angle [R][3] (per ray; N = R*S) -> raw [N][4] = (rgb, sigma). */
 int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const float *feat, const float *angle, int R,
                     int S, float *raw, int mode, void *stream);
+
+/* same network on tile-transposed feature rows (ucn_gather_tiles_from_z); UCN_MLP_BF16X3_TC only */
+int ucn_mlp_forward_tiles(const ucn_weights *w, const float *ndc_pts, const float *feat_tiles, const float *angle,
+                          int R, int S, float *raw, int mode, void *stream);
 
 /* ---- K4: alpha compositing -------------------------------------------------------------------
  * replaces raw2alpha / raw2outputs (network/renderer.py:25-36,109-140).  rgb [R][3], depth [R];

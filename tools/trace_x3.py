@@ -11,14 +11,16 @@ F = 24 + 12 * V + 1
 pw = PackedWeights(synthetic.make_weights(V, seed=0), V, "cuda")
 g = torch.Generator("cuda").manual_seed(0)
 ndc = torch.rand((R * S, 3), device="cuda", generator=g)
-feat = torch.randn((R * S, F), device="cuda", generator=g)
-feat[:, -1] = torch.rand(R * S, device="cuda", generator=g)
+NT = (R * S + 127) // 128
+feat = torch.randn((NT, F, 128), device="cuda", generator=g)          # tile-transposed interchange layout
+feat[:, -1, :] = torch.rand((NT, 128), device="cuda", generator=g)
+lib.ucn_mlp_forward_tiles.argtypes = lib.ucn_mlp_forward.argtypes
 ang = torch.randn((R, 3), device="cuda", generator=g)
 raw = torch.empty((R * S, 4), device="cuda")
 CAP = 2048
 buf = torch.zeros(7 * CAP * 2, dtype=torch.int64, device="cuda")
 def run():
-    L.check(lib.ucn_mlp_forward(C.byref(pw.c), L.ptr(ndc), L.ptr(feat), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
+    L.check(lib.ucn_mlp_forward_tiles(C.byref(pw.c), L.ptr(ndc), L.ptr(feat), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
 flags = int(os.environ.get("X3_DBG", "0"))
 L.check(lib.ucn_debug_set_flags(flags), "flags")
 run(); torch.cuda.synchronize()

@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(128, 1) k_stream(int v, int iters, long long *
   const uint32_t tb = tptr;
   long long t0 = clock64();
   if (warp == 1 && lane == 0) {
-    mbar_arrive(smem_u32(&done));   // phase 0 of `done` completes: try_wait(parity 0) on it always succeeds
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&done)) : "memory");   // phase 0 of `done` completes: try_wait(parity 0) on it always succeeds
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(128 >> 3) << 17) | ((128u >> 4) << 24);
     for (int blk = 0; blk < iters / 6; ++blk) {
       if (v & 4) mbar_wait(smem_u32(&done), 0);

@@ -63,6 +63,17 @@ extern "C" int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const
   return ucn_set_error(UCN_E_ARG, "ucn_mlp_forward: unknown mode");
 }
 
+extern "C" int ucn_mlp_forward_tiles(const ucn_weights *w, const float *ndc_pts, const float *feat_tiles,
+                                     const float *angle, int R, int S, float *raw, int mode, void *stream) {
+  UCN_CHECK_ARG(w && ndc_pts && feat_tiles && angle && raw, "ucn_mlp_forward_tiles: null argument");
+  UCN_CHECK_ARG(w->V >= 1 && w->V <= UCN_MAX_V, "ucn_mlp_forward_tiles: 1 <= V <= 8");
+  UCN_CHECK_ARG(S > 0, "ucn_mlp_forward_tiles: S <= 0");
+  if (mode != UCN_MLP_BF16X3_TC) return ucn_set_error(UCN_E_UNSUPPORTED, "ucn_mlp_forward_tiles: only UCN_MLP_BF16X3_TC reads tiled rows");
+  if (R <= 0) return UCN_OK;
+  const long long F = 24 + 12 * w->V + 1;
+  return ucn_mlp_forward_x3(w, ndc_pts, feat_tiles, 128 * F, 128, 1, angle, R, S, raw, stream);
+}
+
 // workspace carve-up for ucn_render_rays (all 256-byte aligned)
 namespace {
 struct Workspace {
@@ -72,7 +83,7 @@ struct Workspace {
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 255) & ~size_t(255); return r; };
     z = take(N * 4); rays_d = take((size_t)R * 12); angle = take((size_t)R * 12);
-    ndc = take(N * 12); feat = take(N * F * 4); raw = take(N * 16);
+    ndc = take(N * 12); feat = take(((N + 127) / 128) * 128 * F * 4); raw = take(N * 16);   // feat: whole tiles
     total = o;
   }
 };
@@ -99,8 +110,13 @@ extern "C" int ucn_render_rays(const ucn_frame *f, const ucn_weights *w, int ray
   int rc;
   if ((rc = ucn_raygen_sample(f, nullptr, ray0, R, t_vals, t_rand, seed, z, rays_d, nullptr, nullptr, stream))) return rc;
   if ((rc = ucn_dir_feature(f, rays_d, R, ray0, angle, stream))) return rc;
-  if ((rc = ucn_gather_from_z(f, z, nullptr, ray0, R, feat, ndc, stream))) return rc;
-  if ((rc = ucn_mlp_forward(w, ndc, feat, angle, R, f->S, raw, mode, stream))) return rc;
+  if (mode == UCN_MLP_BF16X3_TC) {          // tensor-core path: tile-transposed interchange rows
+    if ((rc = ucn_gather_tiles_from_z(f, z, nullptr, ray0, R, feat, ndc, stream))) return rc;
+    if ((rc = ucn_mlp_forward_tiles(w, ndc, feat, angle, R, f->S, raw, mode, stream))) return rc;
+  } else {
+    if ((rc = ucn_gather_from_z(f, z, nullptr, ray0, R, feat, ndc, stream))) return rc;
+    if ((rc = ucn_mlp_forward(w, ndc, feat, angle, R, f->S, raw, mode, stream))) return rc;
+  }
   if ((rc = ucn_composite(raw, z, R, f->S, 0, out_rgb, out_depth, nullptr, nullptr, stream))) return rc;
   return UCN_OK;
 }

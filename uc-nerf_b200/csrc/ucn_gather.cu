@@ -51,7 +51,7 @@ template <bool FROM_Z>
 __global__ void __launch_bounds__(kThreads)
 gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts_or_z,
               const float *__restrict__ ndc1, const float *__restrict__ ndc2, const float *__restrict__ ndc3,
-              const float *__restrict__ pix_yx, int ray0, int R, int64_t n_samples, int parts,
+              const float *__restrict__ pix_yx, int ray0, int R, int64_t n_samples, int parts, int tiled,
               float *__restrict__ feat, float *__restrict__ ndc_out, int32_t *__restrict__ idx_out) {
   extern __shared__ float rows[];                       // [kThreads][F + 1]  (+1: odd stride, no bank conflicts)
   const int V = f.V, F = 24 + 12 * V + 1, ld = F + 1;
@@ -138,6 +138,17 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
       if (ir) { ir[11 + 3 * v] = ax.i0; ir[12 + 3 * v] = ay.i0; ir[13 + 3 * v] = (int32_t)m; }
     }
   }
+  if (tiled) {
+    // tile-transposed rows for the tensor-core MLP: block == one 128-sample tile, laid out [F][128] so that both
+    // this store and the MLP's per-row loads are one coalesced 128-byte line per warp and channel
+    float *dst = feat + (int64_t)blockIdx.x * F * kThreads + threadIdx.x;
+    if (q < n_samples) {
+      for (int c = 0; c < F; ++c) dst[(int64_t)c * kThreads] = row[c];
+    } else {
+      for (int c = 0; c < F; ++c) dst[(int64_t)c * kThreads] = 0.0f;
+    }
+    return;
+  }
   __syncthreads();
   // coalesced write-out of the block's contiguous [rows_here][F] span
   const int64_t q0 = (int64_t)blockIdx.x * kThreads;
@@ -149,7 +160,7 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
 }  // namespace
 
 static int launch_gather(bool from_z, const ucn_frame *f, const float *a, const float *n1, const float *n2,
-                         const float *n3, const float *pix_yx, int ray0, int R, int64_t n, int parts,
+                         const float *n3, const float *pix_yx, int ray0, int R, int64_t n, int parts, int tiled,
                          float *feat, float *ndc_out, int32_t *idx, void *stream) {
   UCN_CHECK_ARG(f && a && feat, "ucn_gather: null argument");
   UCN_CHECK_ARG(f->V >= 1 && f->V <= UCN_MAX_V, "ucn_gather: 1 <= V <= 8 source views");
@@ -161,12 +172,12 @@ static int launch_gather(bool from_z, const ucn_frame *f, const float *a, const 
     static bool attr = false;
     if (!attr) { cudaFuncSetAttribute(gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; }
     gather_kernel<true><<<blocks, kThreads, smem, (cudaStream_t)stream>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts,
-                                                                         feat, ndc_out, idx);
+                                                                         tiled, feat, ndc_out, idx);
   } else {
     static bool attr = false;
     if (!attr) { cudaFuncSetAttribute(gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; }
     gather_kernel<false><<<blocks, kThreads, smem, (cudaStream_t)stream>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts,
-                                                                          feat, ndc_out, idx);
+                                                                          tiled, feat, ndc_out, idx);
   }
   UCN_LAUNCH_CHECK("gather_kernel");
   return UCN_OK;
@@ -177,15 +188,22 @@ extern "C" int ucn_gather(const ucn_frame *f, const float *pts, const float *ndc
                           void *stream) {
   UCN_CHECK_ARG(ndc_s1 && ndc_s2 && ndc_s3, "ucn_gather: null ndc");
   UCN_CHECK_ARG(parts >= 1 && parts <= 3, "ucn_gather: parts must be 1, 2 or 3");
-  return launch_gather(false, f, pts, ndc_s1, ndc_s2, ndc_s3, nullptr, 0, 0, n_samples, parts, feat, nullptr, idx,
+  return launch_gather(false, f, pts, ndc_s1, ndc_s2, ndc_s3, nullptr, 0, 0, n_samples, parts, 0, feat, nullptr, idx,
                        stream);
 }
 
 extern "C" int ucn_gather_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R,
                                  float *feat, float *ndc_pts, void *stream) {
   UCN_CHECK_ARG(f && f->S > 0, "ucn_gather_from_z: bad frame");
-  return launch_gather(true, f, z, nullptr, nullptr, nullptr, pix_yx, ray0, R, (int64_t)R * f->S, UCN_PART_ALL, feat,
+  return launch_gather(true, f, z, nullptr, nullptr, nullptr, pix_yx, ray0, R, (int64_t)R * f->S, UCN_PART_ALL, 0, feat,
                        ndc_pts, nullptr, stream);
+}
+
+extern "C" int ucn_gather_tiles_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R,
+                                       float *feat_tiles, float *ndc_pts, void *stream) {
+  UCN_CHECK_ARG(f && f->S > 0, "ucn_gather_tiles_from_z: bad frame");
+  return launch_gather(true, f, z, nullptr, nullptr, nullptr, pix_yx, ray0, R, (int64_t)R * f->S, UCN_PART_ALL, 1,
+                       feat_tiles, ndc_pts, nullptr, stream);
 }
 
 namespace {

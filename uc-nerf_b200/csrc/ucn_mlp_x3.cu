@@ -182,7 +182,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
               float *__restrict__ raw) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const ucn::X3Layout L(V);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform by construction
   const int nst = plan.nst, rpt = plan.rpt, nblk = plan.nblk;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t ring = sbase + 2 * SLOT;
@@ -214,7 +214,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(smem + (tmem_ptr_addr - sbase));
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t *>(smem + (tmem_ptr_addr - sbase)), 0);
 
   const long long ntiles = (N + 127) / 128;
   const long long npairs = (ntiles + 1) / 2;
@@ -256,7 +256,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
         const int nslots = (2 * p + 1 < ntiles) ? 2 : 1;
 #pragma unroll 1
         for (int r = 0; r < NROUND; ++r) {
-          const int b0 = rb_s[r], b1 = rb_s[r + 1];
+          const int b0 = plan.round_begin[r], b1 = plan.round_begin[r + 1];
 #pragma unroll 1
           for (int s = 0; s < nslots; ++s) {
             if (s == 0) { mbar_wait(bar_in, ph_in0); ph_in0 ^= 1; } else { mbar_wait(bar_in + 8, ph_in1); ph_in1 ^= 1; }
@@ -268,8 +268,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
             uint32_t st = st0, wph = wph0;
 #pragma unroll 1
             for (int b = b0; b < b1; ++b) {
-              const uint32_t info = blk_s[b];                     // units | a0 << 8 | flags << 16
-              const uint32_t units = info & 0xFF, a0 = (info >> 8) & 0xFF, flags = info >> 16;
+              const uint32_t units = plan.blk[b].units, a0 = plan.blk[b].a0, flags = plan.blk[b].flags;
               const long long w0 = tr.base ? clock64() : 0;
               if (s == 0) mbar_wait(bar_wfull + 8 * st, wph);       // slot 1 reuses the stage slot 0 waited for
               if (tr.base) wwait += clock64() - w0;
@@ -335,12 +334,13 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
     for (long long p = blockIdx.x; p < npairs; p += gridDim.x) {
       const long long tile = 2 * p + s;
       if (tile >= ntiles) break;
-      const long long q = tile * 128 + row;
-      const bool valid = q < N;
-      const long long ray_first = (tile * 128) / S;
-      const long long q_last = (tile * 128 + 127 < N ? tile * 128 + 127 : N - 1);
-      const int nrays_tile = (int)(q_last / S - ray_first) + 1;
-      const int ri = valid ? (int)(q / S - ray_first) : 0;
+      // 32-bit sample / ray arithmetic (the launcher guarantees N < 2^31)
+      const uint32_t q0 = (uint32_t)tile * 128u, q = q0 + row, Nu = (uint32_t)N, Su = (uint32_t)S;
+      const bool valid = q < Nu;
+      const uint32_t ray_first = q0 / Su;
+      const uint32_t q_last = q0 + 127u < Nu ? q0 + 127u : Nu - 1u;
+      const int nrays_tile = (int)(q_last / Su - ray_first) + 1;
+      const int ri = valid ? (int)(q / Su - ray_first) : 0;
       const float *frow = feat + tile * f_tile_stride + (long long)row * f_row_stride;
       // ---- stage inputs: warpgroup 0 -> PE(ndc) in H[0..7]; warpgroup 1 -> [film inputs | 1] in H[8..] ------------
       if (hf == 0) {
@@ -353,14 +353,18 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
         for (int c = 0; c < 8; ++c) store_chunk_x3(h_row, c, pe + 8 * c);
         u = 1.0f - (valid ? __ldg(frow + (F - 1) * f_k_stride) : 0.0f);          // models.py:149
       } else {
-        for (int c = 0; c < L.Kfilm / 8; ++c) {
-          float v[8];
+        // all loads of a 32-channel group are issued before the first use: one memory round trip per group
+#pragma unroll 1
+        for (int g4 = 0; g4 < L.Kfilm / 8; g4 += 4) {
+          float v[32];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int k = 8 * c + i;
-            v[i] = k < Kfilm_real ? (valid ? __ldg(frow + k * f_k_stride) : 0.0f) : (k == Kfilm_real ? 1.0f : 0.0f);
+          for (int i = 0; i < 32; ++i) {
+            const int k = 8 * g4 + i;
+            v[i] = (k < Kfilm_real && valid) ? __ldg(frow + k * f_k_stride) : (k == Kfilm_real ? 1.0f : 0.0f);
           }
-          store_chunk_x3(h_row, 8 + c, v);
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            if (g4 + c < L.Kfilm / 8) store_chunk_x3(h_row, 8 + g4 + c, v + 8 * c);
         }
       }
       arrive_in();
@@ -418,7 +422,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
           epi64<1, false>(t_acc, t_mod, col0, f32s + ucn::X3Layout::b_feat, nullptr, h_row, nullptr, head);
           // per-ray view-direction term of views|view_confi: column `row`, rays hf, hf+2, ... of this tile
           for (int i = hf; i < nrays_tile; i += 2) {
-            const long long ray = ray_first + i;
+            const uint32_t ray = ray_first + i;
             const float a[3] = {__ldg(angle + 3 * ray), __ldg(angle + 3 * ray + 1), __ldg(angle + 3 * ray + 2)};
             float pe[27];
             pos_enc<4>(a, pe);
@@ -526,6 +530,7 @@ int ucn_mlp_forward_x3(const ucn_weights *w, const float *ndc_pts, const float *
   if (rc == -2) return ucn_set_error(UCN_E_UNSUPPORTED, "ucn_mlp_forward: BF16X3_TC needs S >= 7 samples per ray (shared-memory budget)");
   if (rc != 0) return ucn_set_error(UCN_E_ARG, "ucn_mlp_forward: cannot build the x3 schedule");
   const long long N = (long long)R * S;
+  UCN_CHECK_ARG(N < (1ll << 31), "ucn_mlp_forward: more than 2^31 samples in one call; split the ray range");
   static int attr_bytes = 0;
   if (attr_bytes < (int)P.smem_total) {
     cudaError_t e = cudaFuncSetAttribute(mlp_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.smem_total);

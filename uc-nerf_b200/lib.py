@@ -62,6 +62,8 @@ _SIGS = {
     "ucn_project_points": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_int, C.c_int, _fp, C.c_int64,
                                      _fp, _fp]),
     "ucn_gather_from_z": (C.c_int, [C.POINTER(Frame), _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp]),
+    "ucn_gather_tiles_from_z": (C.c_int, [C.POINTER(Frame), _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp]),
+    "ucn_mlp_forward_tiles": (C.c_int, [C.POINTER(Weights), _fp, _fp, _fp, C.c_int, C.c_int, _fp, C.c_int, _fp]),
     "ucn_dir_feature": (C.c_int, [C.POINTER(Frame), _fp, C.c_int, C.c_int, _fp, _fp]),
     "ucn_mlp_forward": (C.c_int, [C.POINTER(Weights), _fp, _fp, _fp, C.c_int, C.c_int, _fp, C.c_int, _fp]),
     "ucn_composite": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, _fp]),
