@@ -10,7 +10,10 @@ hdr = rows[hi]
 i_s, i_src = hdr.index("# Samples"), hdr.index("Source")
 stall = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
 tot = collections.Counter()
-body = [r for r in rows[hi + 1:] if len(r) == len(hdr)]
+body = []
+for r in rows[hi + 1:]:
+    if r and r[0] == "Address": break          # next kernel instance
+    if len(r) == len(hdr): body.append(r)
 for r in body:
     for i in stall:
         try: tot[hdr[i]] += int(r[i] or 0)

@@ -82,84 +82,67 @@ struct Plan {
   uint32_t off_f32, off_exch, off_rayb, off_bars, smem_total;   // shared-memory carve-up after the ring
 };
 
-// Epilogue of 32 columns [c0, c0+32) of a 128-wide round for this thread's row.
+// Epilogue of one 64-column half of a 128-wide round, 32 columns at a time.
 //   MODE 0: relu((acc + b) * mod) -> H          pts layers                          (models.py:154-155)
 //   MODE 1: acc + b -> H                        feature_linear                      (models.py:164)
 //   MODE 2: relu(acc + b + ray term), no store  views / view_confi hidden           (models.py:168-173)
 //   MODE 3: h(smem) * mod -> H                  h * feats_bias, bias folded in MMA  (models.py:164)
-// HEADS (fp32 dot products on the CUDA cores, accumulated over this thread's columns):
-//   4: head[0..3] += v[c] * w4[c][0..3]   (confi_rgb_linear | alpha_linear_1, or rgb_linear with a zero 4th column)
-//   1: head[3]    += v[c] * w1[c - 64]    (alpha_linear: columns 64..127 feed only sigma)
-template <int MODE, int HEADS>
-__device__ __forceinline__ void epi32(uint32_t t_acc, uint32_t t_mod, int c0, const float *__restrict__ bias,
-                                      const float *__restrict__ rayb, uint32_t h_row, const float *__restrict__ wh,
-                                      float (&head)[4]) {
-  uint32_t a[32], m[32];
-  if (MODE != 3) tmem_ld32(t_acc + c0, a);
-  if (MODE == 0 || MODE == 3) tmem_ld32(t_mod + c0, m);
-  tmem_wait_ld();
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int c = c0 + 8 * j;
-    float v[8];
-    float4 w4[HEADS == 4 ? 8 : 1];
-    float4 w1[HEADS == 1 ? 2 : 1];
-    if (HEADS == 4) {                       // weights first: their latency hides behind the bias/FiLM arithmetic
-#pragma unroll
-      for (int i = 0; i < 8; ++i) w4[i] = *reinterpret_cast<const float4 *>(wh + 4 * (c + i));
-    }
-    if (HEADS == 1) { w1[0] = *reinterpret_cast<const float4 *>(wh + c - 64); w1[1] = *reinterpret_cast<const float4 *>(wh + c - 60); }
-    if (MODE == 3) {
-      const uint4 oh = lds128(h_row + (c >> 3) * CHUNK), ol = lds128(h_row + HALF + (c >> 3) * CHUNK);
-      const uint32_t xh[4] = {oh.x, oh.y, oh.z, oh.w}, xl[4] = {ol.x, ol.y, ol.z, ol.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        v[2 * i] = (bf_lo(xh[i]) + bf_lo(xl[i])) * __uint_as_float(m[8 * j + 2 * i]);
-        v[2 * i + 1] = (bf_hi(xh[i]) + bf_hi(xl[i])) * __uint_as_float(m[8 * j + 2 * i + 1]);
-      }
-    } else {
-      const float4 b0 = *reinterpret_cast<const float4 *>(bias + c), b1 = *reinterpret_cast<const float4 *>(bias + c + 4);
-      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-      float rb[8];
-      if (MODE == 2) {
-        const float4 r0 = *reinterpret_cast<const float4 *>(rayb + c), r1 = *reinterpret_cast<const float4 *>(rayb + c + 4);
-        rb[0] = r0.x; rb[1] = r0.y; rb[2] = r0.z; rb[3] = r0.w; rb[4] = r1.x; rb[5] = r1.y; rb[6] = r1.z; rb[7] = r1.w;
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float x = __uint_as_float(a[8 * j + i]) + bb[i];
-        if (MODE == 0) v[i] = fmaxf(x * __uint_as_float(m[8 * j + i]), 0.0f);
-        if (MODE == 1) v[i] = x;
-        if (MODE == 2) v[i] = fmaxf(x + rb[i], 0.0f);
-      }
-    }
-    if (HEADS == 4) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        head[0] = fmaf(v[i], w4[i].x, head[0]); head[1] = fmaf(v[i], w4[i].y, head[1]);
-        head[2] = fmaf(v[i], w4[i].z, head[2]); head[3] = fmaf(v[i], w4[i].w, head[3]);
-      }
-    }
-    if (HEADS == 1) {
-      const float ww[8] = {w1[0].x, w1[0].y, w1[0].z, w1[0].w, w1[1].x, w1[1].y, w1[1].z, w1[1].w};
-#pragma unroll
-      for (int i = 0; i < 8; ++i) head[i & 3] = fmaf(v[i], ww[i], head[i & 3]);   // 4 partial sums, folded by the caller
-    }
-    if (MODE != 2) {
-      uint32_t hi[4], lo[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) split2(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
-      sts128(h_row + (c >> 3) * CHUNK, hi[0], hi[1], hi[2], hi[3]);
-      sts128(h_row + HALF + (c >> 3) * CHUNK, lo[0], lo[1], lo[2], lo[3]);
-    }
-  }
-}
-template <int MODE, int HEADS>
+// HEADS: accumulate the 4-wide head  head4 += v[c] * w4[c]  (fp32, CUDA cores) for this thread's 64 columns.
+template <int MODE, bool HEADS>
 __device__ __forceinline__ void epi64(uint32_t t_acc, uint32_t t_mod, int col0, const float *__restrict__ bias,
-                                      const float *__restrict__ rayb, uint32_t h_row, const float *__restrict__ wh,
+                                      const float *__restrict__ rayb, uint32_t h_row, const float *__restrict__ w4,
                                       float (&head)[4]) {
 #pragma unroll 1
-  for (int c0 = col0; c0 < col0 + 64; c0 += 32) epi32<MODE, HEADS>(t_acc, t_mod, c0, bias, rayb, h_row, wh, head);
+  for (int c0 = col0; c0 < col0 + 64; c0 += 32) {
+    uint32_t a[32], m[32];
+    if (MODE != 3) tmem_ld32(t_acc + c0, a);
+    if (MODE == 0 || MODE == 3) tmem_ld32(t_mod + c0, m);
+    tmem_wait_ld();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c0 + 8 * j;
+      float v[8];
+      if (MODE == 3) {
+        const uint4 oh = lds128(h_row + (c >> 3) * CHUNK), ol = lds128(h_row + HALF + (c >> 3) * CHUNK);
+        const uint32_t wh[4] = {oh.x, oh.y, oh.z, oh.w}, wl[4] = {ol.x, ol.y, ol.z, ol.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          v[2 * i] = (bf_lo(wh[i]) + bf_lo(wl[i])) * __uint_as_float(m[8 * j + 2 * i]);
+          v[2 * i + 1] = (bf_hi(wh[i]) + bf_hi(wl[i])) * __uint_as_float(m[8 * j + 2 * i + 1]);
+        }
+      } else {
+        const float4 b0 = *reinterpret_cast<const float4 *>(bias + c), b1 = *reinterpret_cast<const float4 *>(bias + c + 4);
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        float rb[8];
+        if (MODE == 2) {
+          const float4 r0 = *reinterpret_cast<const float4 *>(rayb + c), r1 = *reinterpret_cast<const float4 *>(rayb + c + 4);
+          rb[0] = r0.x; rb[1] = r0.y; rb[2] = r0.z; rb[3] = r0.w; rb[4] = r1.x; rb[5] = r1.y; rb[6] = r1.z; rb[7] = r1.w;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float x = __uint_as_float(a[8 * j + i]) + bb[i];
+          if (MODE == 0) v[i] = fmaxf(x * __uint_as_float(m[8 * j + i]), 0.0f);
+          if (MODE == 1) v[i] = x;
+          if (MODE == 2) v[i] = fmaxf(x + rb[i], 0.0f);
+        }
+      }
+      if (HEADS) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 w = *reinterpret_cast<const float4 *>(w4 + 4 * (c + i));
+          head[0] = fmaf(v[i], w.x, head[0]); head[1] = fmaf(v[i], w.y, head[1]);
+          head[2] = fmaf(v[i], w.z, head[2]); head[3] = fmaf(v[i], w.w, head[3]);
+        }
+      }
+      if (MODE != 2) {
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) split2(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+        sts128(h_row + (c >> 3) * CHUNK, hi[0], hi[1], hi[2], hi[3]);
+        sts128(h_row + HALF + (c >> 3) * CHUNK, lo[0], lo[1], lo[2], lo[3]);
+      }
+    }
+  }
 }
 
 // write 8 consecutive K values (one chunk) of this thread's row as hi/lo bf16
@@ -190,19 +173,7 @@ __device__ __forceinline__ void pos_enc(const float (&x)[3], float *pe) {
     }
   }
 }
-// PE(ndc) -> chunks [4*half, 4*half+4) of this row's H region (hi/lo); the two warpgroups of a slot take one half each
-__device__ __forceinline__ void stage_pe_half(const float (&x)[3], int half, uint32_t h_row) {
-  float pe[64];
-  pos_enc<10>(x, pe);
-  pe[63] = 0.0f;
-  if (half == 0) {
-#pragma unroll
-    for (int c = 0; c < 4; ++c) store_chunk_x3(h_row, c, pe + 8 * c);
-  } else {
-#pragma unroll
-    for (int c = 4; c < 8; ++c) store_chunk_x3(h_row, c, pe + 8 * c);
-  }
-}
+
 
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict__ wpack, int V,
@@ -281,7 +252,6 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
       Tracer tr(0);
       if (lane != 0) tr.base = nullptr;
       const uint32_t ring_lo = dlo + (ring >> 4);
-      const uint32_t ts_lo = L.Kfb <= 32 ? 16u : 32u;             // TMEM column distance hi -> lo words of the fb operand
       for (long long p = blockIdx.x; p < npairs; p += gridDim.x) {
         const int nslots = (2 * p + 1 < ntiles) ? 2 : 1;
 #pragma unroll 1
@@ -308,13 +278,13 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
               const uint32_t d = t_slot + ((flags & BF_MOD) ? 0 : 128);
               const uint32_t first = (flags & BF_FRESH) ? 0u : 1u;
               if (flags & BF_TS) {
-                const uint32_t ah = t_slot + 128 + 64 + 8 * a0, al = ah + ts_lo;
+                const uint32_t ah = t_slot + 128 + 64 + 8 * a0;
                 umma_ts_w(d, ah, mk(b_lo), idesc, first);
-                umma_ts_w(d, al, mk(b_lo), idesc, 1u);
+                umma_ts_w(d, ah + 32, mk(b_lo), idesc, 1u);
                 umma_ts_w(d, ah, mk(b_lo + 256), idesc, 1u);
                 if (units > 1) {
                   umma_ts_w(d, ah + 8, mk(b_lo + 512), idesc, 1u);
-                  umma_ts_w(d, al + 8, mk(b_lo + 512), idesc, 1u);
+                  umma_ts_w(d, ah + 40, mk(b_lo + 512), idesc, 1u);
                   umma_ts_w(d, ah + 8, mk(b_lo + 768), idesc, 1u);
                 }
               } else {
@@ -350,7 +320,6 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
     const int col0 = 64 * hf, bar_id = 1 + s;
     const uint32_t my_acc = pin(bar_acc + 8 * s), my_in = pin(bar_in + 8 * s);
     const float *bias_s = f32s + ucn::X3Layout::b_pts;
-    const bool fb_stash = L.Kfb <= 32;          // V <= 3: the fb operand fits the 32 columns freed first in round 6
     uint32_t ph_acc = 0;
     Tracer tr(((warp & 3) == 0 && lane == 0) ? 1 + g : 6);
     if (!((warp & 3) == 0 && lane == 0)) tr.base = nullptr;
@@ -373,12 +342,16 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
       const int nrays_tile = (int)(q_last / Su - ray_first) + 1;
       const int ri = valid ? (int)(q / Su - ray_first) : 0;
       const float *frow = feat + tile * f_tile_stride + (long long)row * f_row_stride;
-      // ---- stage inputs: PE(ndc) -> H[0..7] (half per warpgroup); warpgroup 1 also [film inputs | 1] -> H[8..] ---
-      if (valid) { x[0] = __ldg(ndc_pts + 3 * q); x[1] = __ldg(ndc_pts + 3 * q + 1); x[2] = __ldg(ndc_pts + 3 * q + 2); }
-      else { x[0] = x[1] = x[2] = 0.f; }
+      // ---- stage inputs: warpgroup 0 -> PE(ndc) in H[0..7]; warpgroup 1 -> [film inputs | 1] in H[8..] ------------
       if (hf == 0) {
+        if (valid) { x[0] = ndc_pts[3 * q]; x[1] = ndc_pts[3 * q + 1]; x[2] = ndc_pts[3 * q + 2]; }
+        else { x[0] = x[1] = x[2] = 0.f; }
+        float pe[64];
+        pos_enc<10>(x, pe);
+        pe[63] = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) store_chunk_x3(h_row, c, pe + 8 * c);
         u = 1.0f - (valid ? __ldg(frow + (F - 1) * f_k_stride) : 0.0f);          // models.py:149
-        stage_pe_half(x, 0, h_row);
       } else {
         // all loads of a 32-channel group are issued before the first use: one memory round trip per group
 #pragma unroll 1
@@ -389,7 +362,6 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
             const int k = 8 * g4 + i;
             v[i] = (k < Kfilm_real && valid) ? __ldg(frow + k * f_k_stride) : (k == Kfilm_real ? 1.0f : 0.0f);
           }
-          if (g4 == 0) stage_pe_half(x, 1, h_row);                               // overlaps the loads' latency
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             if (g4 + c < L.Kfilm / 8) store_chunk_x3(h_row, 8 + g4 + c, v + 8 * c);
@@ -406,55 +378,22 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
         if (dbg & 2) {
           // experiment: no epilogue work at all
         } else if (r < 5) {
-          epi64<0, 0>(t_acc, t_mod, col0, bias_s + 128 * r, nullptr, h_row, nullptr, head);
+          epi64<0, false>(t_acc, t_mod, col0, bias_s + 128 * r, nullptr, h_row, nullptr, head);
         } else if (r == 5) {
-          // skip connection: PE back into H[0..7] (half per warpgroup).  Warpgroup 1 also fetches [img feats | 1],
-          // splits it and parks the words in its own rows of H[12..15] (dead until round 6 rewrites them): the
-          // loads' latency is paid here, where this warpgroup has nothing else to do.
-          if (hf == 1 && fb_stash) {
-            float v[32];
+          if (hf == 0) {                                         // skip connection: PE back into H[0..7]
+            float pe[64];
+            pos_enc<10>(x, pe);
+            pe[63] = 0.0f;
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
-              v[i] = (i < Kfb_real && valid) ? __ldg(frow + (Kfilm_real + i) * f_k_stride) : (i == Kfb_real ? 1.0f : 0.0f);
-            stage_pe_half(x, 1, h_row);
-#pragma unroll
-            for (int c = 0; c < 4; ++c) store_chunk_x3(h_row, 12 + c, v + 8 * c);   // hi words -> H_hi[12+c], lo -> H_lo[12+c]
-          } else {
-            stage_pe_half(x, hf, h_row);
+            for (int c = 0; c < 8; ++c) store_chunk_x3(h_row, c, pe + 8 * c);
           }
         } else if (r == 6) {
           head[0] = head[1] = head[2] = head[3] = 0.f;
-          if (hf == 0) {
-            epi64<0, 4>(t_acc, t_mod, col0, bias_s + 128 * 5, nullptr, h_row, f32s + ucn::X3Layout::w_base, head);
-            named_bar_sync(bar_id, 256);
-            const float4 o = exch_s[s * 128 + row];
-            const float *bb = f32s + ucn::X3Layout::b_base;
-            base4[0] = head[0] + o.x + bb[0]; base4[1] = head[1] + o.y + bb[1];
-            base4[2] = head[2] + o.z + bb[2]; base4[3] = head[3] + o.w + bb[3];
-          } else if (fb_stash) {
-            // columns 64..95 first; their accumulator columns are then free to take the fb A operand (hi words ->
-            // acc columns 64..79, lo words -> 80..95) before columns 96..127 overwrite the parked words in H[12..15]
-            epi32<0, 4>(t_acc, t_mod, 64, bias_s + 128 * 5, nullptr, h_row, f32s + ucn::X3Layout::w_base, head);
-            {
-              uint32_t hi[16], lo[16];
-#pragma unroll
-              for (int c = 0; c < 4; ++c) {
-                const uint4 a4 = lds128(h_row + (12 + c) * CHUNK), b4 = lds128(h_row + HALF + (12 + c) * CHUNK);
-                hi[4 * c] = a4.x; hi[4 * c + 1] = a4.y; hi[4 * c + 2] = a4.z; hi[4 * c + 3] = a4.w;
-                lo[4 * c] = b4.x; lo[4 * c + 1] = b4.y; lo[4 * c + 2] = b4.z; lo[4 * c + 3] = b4.w;
-              }
-              tmem_st16(t_acc + 64, hi);
-              tmem_st16(t_acc + 80, lo);
-            }
-            epi32<0, 4>(t_acc, t_mod, 96, bias_s + 128 * 5, nullptr, h_row, f32s + ucn::X3Layout::w_base, head);
+          epi64<0, true>(t_acc, t_mod, col0, bias_s + 128 * 5, nullptr, h_row, f32s + ucn::X3Layout::w_base, head);
+          if (hf == 1) {
             exch_s[s * 128 + row] = make_float4(head[0], head[1], head[2], head[3]);
             named_bar_arrive(bar_id, 256);
-            tmem_wait_st();
-          } else {
-            epi64<0, 4>(t_acc, t_mod, col0, bias_s + 128 * 5, nullptr, h_row, f32s + ucn::X3Layout::w_base, head);
-            exch_s[s * 128 + row] = make_float4(head[0], head[1], head[2], head[3]);
-            named_bar_arrive(bar_id, 256);
-            // more than 32 fb inputs (V >= 4): fetch and split them here; hi words -> acc columns 64.., lo -> 96..
+            // [img feats | 1] as split bf16 pairs -> TMEM acc columns 64.. (hi) and 96.. (lo): A operand of fb
 #pragma unroll 1
             for (int h16 = 0; h16 < 2; ++h16) {
               uint32_t hi[16], lo[16];
@@ -470,11 +409,17 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
               tmem_st16(t_acc + 96 + 16 * h16, lo);
             }
             tmem_wait_st();
+          } else {
+            named_bar_sync(bar_id, 256);
+            const float4 o = exch_s[s * 128 + row];
+            const float *bb = f32s + ucn::X3Layout::b_base;
+            base4[0] = head[0] + o.x + bb[0]; base4[1] = head[1] + o.y + bb[1];
+            base4[2] = head[2] + o.z + bb[2]; base4[3] = head[3] + o.w + bb[3];
           }
         } else if (r == 7) {
-          epi64<3, 0>(t_acc, t_mod, col0, nullptr, nullptr, h_row, nullptr, head);
+          epi64<3, false>(t_acc, t_mod, col0, nullptr, nullptr, h_row, nullptr, head);
         } else if (r == 8) {
-          epi64<1, 0>(t_acc, t_mod, col0, f32s + ucn::X3Layout::b_feat, nullptr, h_row, nullptr, head);
+          epi64<1, false>(t_acc, t_mod, col0, f32s + ucn::X3Layout::b_feat, nullptr, h_row, nullptr, head);
           // per-ray view-direction term of views|view_confi: column `row`, rays hf, hf+2, ... of this tile
           for (int i = hf; i < nrays_tile; i += 2) {
             const uint32_t ray = ray_first + i;
@@ -489,15 +434,8 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
           named_bar_sync(bar_id, 256);
         } else {
           head[0] = head[1] = head[2] = head[3] = 0.f;
-          if (hf == 0) {      // columns 0..63 = views hidden -> rgb_linear (3 outputs; the 4th weight column is zero)
-            epi64<2, 4>(t_acc, t_mod, col0, f32s + ucn::X3Layout::b_vv, rayb_s + (s * rpt + ri) * 128, h_row,
-                        f32s + ucn::X3Layout::w_adapt, head);
-          } else {            // columns 64..127 = view_confi hidden -> alpha_linear (1 output)
-            epi64<2, 1>(t_acc, t_mod, col0, f32s + ucn::X3Layout::b_vv, rayb_s + (s * rpt + ri) * 128, h_row,
-                        f32s + ucn::X3Layout::w_alpha, head);
-            head[3] = (head[0] + head[1]) + (head[2] + head[3]);
-            head[0] = head[1] = head[2] = 0.f;
-          }
+          epi64<2, true>(t_acc, t_mod, col0, f32s + ucn::X3Layout::b_vv, rayb_s + (s * rpt + ri) * 128, h_row,
+                         f32s + ucn::X3Layout::w_adapt, head);
           if (hf == 1) {
             exch_s[s * 128 + row] = make_float4(head[0], head[1], head[2], head[3]);
             named_bar_arrive(bar_id, 256);

@@ -140,9 +140,8 @@ static int pack_weights_x3(const ucn_state_dict *sd, unsigned char *dst, cudaStr
   pack_w_f32_kernel<<<2, 256, 0, st>>>(sd->crgb_w, 3, 128, f32 + X.w_base, 4, 0, 0, INT_MAX);
   pack_w_f32_kernel<<<1, 256, 0, st>>>(sd->alpha1_w, 1, 128, f32 + X.w_base, 4, 3, 0, INT_MAX);
   pack_w_f32_kernel<<<1, 256, 0, st>>>(sd->rgb_w, 3, 64, f32 + X.w_adapt, 4, 0, 0, INT_MAX);
-  // alpha_linear reads only the view_confi half (columns 64..127): its 64 weights are kept contiguous
-  cudaMemcpyAsync(f32 + X.w_alpha, sd->alpha_w, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st);
-  ucn_count_launch(3);
+  pack_w_f32_kernel<<<1, 256, 0, st>>>(sd->alpha_w, 1, 64, f32 + X.w_adapt, 4, 3, 64, INT_MAX);
+  ucn_count_launch(4);
   vec(sd->crgb_b, 3, X.b_base); vec(sd->alpha1_b, 1, X.b_base + 3);
   vec(sd->rgb_b, 3, X.b_adapt); vec(sd->alpha_b, 1, X.b_adapt + 3);
   // vd[k][n] = W[n][128 + k]: rows 128..154 of the K dimension of views_linears.0 / view_confi_linears.0

@@ -78,16 +78,16 @@ struct BF16Layout {
 //   pts0 [64]  pts1..4 [128]  pts5h [128] (skip layer, hidden part)  pts5pe [64] (skip layer, PE part)
 //   fb [Kfb] (bias row at k = 8V)   feat [128]   vvh [128] (views|view_confi on the feature part)
 // followed by an fp32 block: b_pts[6*128] b_feat[128] b_vv[128] w_base[128][4] w_adapt[128][4] b_base[4]
-// b_adapt[4] w_alpha[64] (kSmemFloats floats, copied to shared memory) and vd[28][128] (view-direction rows of
+// b_adapt[4] (kSmemFloats floats, copied to shared memory) and vd[28][128] (view-direction rows of
 // views|view_confi, applied per ray on the CUDA cores).
 struct X3Layout {
   static constexpr int kUnit = 8192;
-  static constexpr int kSmemFloats = 6 * 128 + 128 + 128 + 512 + 512 + 4 + 4 + 64;
+  static constexpr int kSmemFloats = 6 * 128 + 128 + 128 + 512 + 512 + 4 + 4;
   int V, Kfilm, Kfb;
   size_t film, pts0, pts14[4], pts5h, pts5pe, fb, feat, vvh, f32, total_bytes;   // byte offsets
   // float offsets inside the fp32 block
   static constexpr int b_pts = 0, b_feat = 768, b_vv = 896, w_base = 1024, w_adapt = 1536, b_base = 2048,
-                       b_adapt = 2052, w_alpha = 2056, vd = 2120;
+                       b_adapt = 2052, vd = 2056;
   __host__ __device__ explicit X3Layout(int V_) : V(V_) {
     Kfilm = (24 + 4 * V_ + 1 + 15) & ~15;
     Kfb = (8 * V_ + 1 + 15) & ~15;
