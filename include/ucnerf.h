@@ -47,7 +47,7 @@ enum { UCN_MLP_FP32 = 0, UCN_MLP_BF16_TC = 1, UCN_MLP_BF16X3_TC = 2 };
 /* One target view ("frame"): cameras by value, packed maps by device pointer.
  * Packed layouts (produced by ucn_pack_*):
  *   nearfar[k] : [h_k][w_k][2]        first / last depth-hypothesis plane of stage k
- *   vol[k]     : [D_k][h_k][w_k][8]   channels-last cost-feature volume of stage k
+ *   vol[k]     : [h_k][w_k][D_k][8]   cost-feature volume of stage k, depth innermost then channels (ucn_pack_volume)
  *   conf       : [H][W]               photometric confidence (as is)
  *   rgb        : [V][H][W][4]         source images, rgb + zero pad
  *   feat       : [V][H][W][8]         source FPN features, channels-last                        */
@@ -109,6 +109,10 @@ int ucn_check_device(void);
  * relayout that lets the gathers below issue one 16/32-byte vector load per texel instead of C
  * channel-strided 4-byte loads (NCDHW: utils/utils.py:869-890; NCHW: :776-788). */
 int ucn_pack_channels_last(const float *src, float *dst, int B, int Cn, int64_t N, int Cpad, void *stream);
+/* feature volume NCDHW [8][D][h][w] -> [h][w][D][8] (outputs['stageK']['volume_feature_no_ref'],
+ * network/mvs_models.py:649,741-746): all samples of a ray stay in the same <=4 (x,y) columns of the target-frustum
+ * volume (utils/utils.py:852-857), so depth-innermost turns the trilinear gather of a warp into contiguous runs. */
+int ucn_pack_volume(const float *src, float *dst, int D, int h, int w, void *stream);
 /* depth_values [D][h][w] -> [h][w][2] = (plane 0, plane D-1)   (utils/utils.py:668-683) */
 int ucn_pack_nearfar(const float *depth_values, float *dst, int D, int h, int w, void *stream);
 size_t ucn_weights_f32_bytes(int V);

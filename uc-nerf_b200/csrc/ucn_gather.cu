@@ -5,9 +5,13 @@
 //   :323-347 get_ndc_coordinate(sample_2d=True); network/renderer.py:177-212 gen_pts_feats.
 //
 // Data layout (see ucn_pack.cu): all maps are channels-last so one texel is one 16/32-byte vector load
-// (volume/feature texel = 8 fp32 = one 32 B sector; rgb texel = float4).  One thread owns one sample;
-// a 128-thread block stages its 128 feature rows in shared memory and writes them out as one
-// contiguous, fully coalesced 128*F*4-byte span.
+// (volume/feature texel = 8 fp32 = one 32 B sector; rgb texel = float4); volumes are [h][w][D][8], depth
+// innermost, because the 32 consecutive samples of a ray that a warp owns share their (x,y) columns and differ
+// only in depth: their corner texels are then neighbours in memory (a few 128-byte lines per load instruction
+// instead of one line per lane).  One thread owns one sample.  Row-major output ([N][F], the reference layout):
+// a 128-thread block stages its rows in shared memory and writes one contiguous 128*F*4-byte span.  Tiled output
+// ([tile][F][128], the tensor-core MLP's interchange layout): every channel is stored straight from registers,
+// one coalesced 128-byte line per warp and channel, no shared memory.
 //
 // Roofline: HBM-bound in this staged form.  Algorithmic bytes per sample = 4F (row out) + 12 (ndc out)
 // + 4 (z in) = 4F+16, plus the maps once per frame (they are L2-resident: 62 MB at 320x256).
@@ -27,9 +31,9 @@ __device__ __forceinline__ void fma8(Acc8 &a, const float *__restrict__ texel, f
   a.v[6] = fmaf(hi.z, w, a.v[6]); a.v[7] = fmaf(hi.w, w, a.v[7]);
 }
 
-// trilinear, border padding, align_corners=False, over a [D][h][w][8] volume
+// trilinear, border padding, align_corners=False, over a [h][w][D][8] volume; channel c -> out[c * os]
 __device__ __forceinline__ void tri8(const float *__restrict__ vol, int D, int h, int w, float cx, float cy, float cz,
-                                     float *__restrict__ out, int32_t *__restrict__ idx) {
+                                     float *__restrict__ out, int os, int32_t *__restrict__ idx) {
   const ucn::Lerp1 ax = ucn::axis(ucn::to_grid(cx), w, false);
   const ucn::Lerp1 ay = ucn::axis(ucn::to_grid(cy), h, false);
   const ucn::Lerp1 az = ucn::axis(ucn::to_grid(cz), D, false);
@@ -40,11 +44,11 @@ __device__ __forceinline__ void tri8(const float *__restrict__ vol, int D, int h
     const int dx = c & 1, dy = (c >> 1) & 1, dz = c >> 2;
     if ((dx && !ax.has1) || (dy && !ay.has1) || (dz && !az.has1)) continue;
     const float wgt = __fmul_rn(__fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0), dz ? az.w1 : az.w0);
-    const size_t t = ((size_t)(az.i0 + dz) * h + (ay.i0 + dy)) * w + (ax.i0 + dx);
+    const size_t t = ((size_t)(ay.i0 + dy) * w + (ax.i0 + dx)) * D + (az.i0 + dz);
     fma8(a, vol + t * 8, wgt);
   }
 #pragma unroll
-  for (int c = 0; c < 8; ++c) out[c] = a.v[c];
+  for (int c = 0; c < 8; ++c) out[c * os] = a.v[c];
 }
 
 template <bool FROM_Z>
@@ -56,7 +60,10 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
   extern __shared__ float rows[];                       // [kThreads][F + 1]  (+1: odd stride, no bank conflicts)
   const int V = f.V, F = 24 + 12 * V + 1, ld = F + 1;
   const int64_t q = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-  float *row = rows + (size_t)threadIdx.x * ld;
+  // channel c of this sample goes to row[c * os]: shared-memory staging row, or (tiled) straight to the
+  // [F][128] tile of this block in global memory
+  const int os = tiled ? kThreads : 1;
+  float *row = tiled ? feat + (int64_t)blockIdx.x * F * kThreads + threadIdx.x : rows + (size_t)threadIdx.x * ld;
   if (q < n_samples) {
     const float iw = (float)(f.W - 1), ih = (float)(f.H - 1);
     float p[3], c1[3], c2[3], c3[3];
@@ -89,13 +96,13 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
     }
     int32_t *ir = idx_out ? idx_out + q * (11 + 3 * V) : nullptr;
     if (parts != UCN_PART_ALL) {
-      for (int c = 0; c < F; ++c) row[c] = 0.0f;
+      for (int c = 0; c < F; ++c) row[c * os] = 0.0f;
       if (ir) for (int c = 0; c < 11 + 3 * V; ++c) ir[c] = 0;
     }
     if (parts & UCN_PART_VOLUMES) {
-    tri8(f.vol[0], f.D[0], f.h[0], f.w[0], c1[0], c1[1], c1[2], row, ir);
-    tri8(f.vol[1], f.D[1], f.h[1], f.w[1], c2[0], c2[1], c2[2], row + 8, ir ? ir + 3 : nullptr);
-    tri8(f.vol[2], f.D[2], f.h[2], f.w[2], c3[0], c3[1], c3[2], row + 16, ir ? ir + 6 : nullptr);
+    tri8(f.vol[0], f.D[0], f.h[0], f.w[0], c1[0], c1[1], c1[2], row, os, ir);
+    tri8(f.vol[1], f.D[1], f.h[1], f.w[1], c2[0], c2[1], c2[2], row + 8 * os, os, ir ? ir + 3 : nullptr);
+    tri8(f.vol[2], f.D[2], f.h[2], f.w[2], c3[0], c3[1], c3[2], row + 16 * os, os, ir ? ir + 6 : nullptr);
     {   // confidence: depth-1 "volume" => bilinear, align_corners=False (renderer.py:195, utils.py:859-865)
       const ucn::Lerp1 ax = ucn::axis(ucn::to_grid(c3[0]), f.W, false), ay = ucn::axis(ucn::to_grid(c3[1]), f.H, false);
       float acc = 0.0f;
@@ -106,7 +113,7 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
         acc = fmaf(__ldg(f.conf + (size_t)(ay.i0 + dy) * f.W + ax.i0 + dx),
                    __fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0), acc);
       }
-      row[F - 1] = acc;
+      row[(F - 1) * os] = acc;
       if (ir) { ir[9] = ax.i0; ir[10] = ay.i0; }
     }
     }
@@ -130,23 +137,19 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
         c.x = fmaf(px.x, wgt, c.x); c.y = fmaf(px.y, wgt, c.y); c.z = fmaf(px.z, wgt, c.z);
         fma8(a, ft + t * 8, wgt);
       }
-      float *o = row + 24 + 4 * v;
-      o[0] = c.x; o[1] = c.y; o[2] = c.z; o[3] = m;
-      float *of = row + 24 + 4 * V + 8 * v;
+      float *o = row + (24 + 4 * v) * os;
+      o[0] = c.x; o[os] = c.y; o[2 * os] = c.z; o[3 * os] = m;
+      float *of = row + (24 + 4 * V + 8 * v) * os;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) of[k] = a.v[k];
+      for (int k = 0; k < 8; ++k) of[k * os] = a.v[k];
       if (ir) { ir[11 + 3 * v] = ax.i0; ir[12 + 3 * v] = ay.i0; ir[13 + 3 * v] = (int32_t)m; }
     }
   }
   if (tiled) {
     // tile-transposed rows for the tensor-core MLP: block == one 128-sample tile, laid out [F][128] so that both
-    // this store and the MLP's per-row loads are one coalesced 128-byte line per warp and channel
-    float *dst = feat + (int64_t)blockIdx.x * F * kThreads + threadIdx.x;
-    if (q < n_samples) {
-      for (int c = 0; c < F; ++c) dst[(int64_t)c * kThreads] = row[c];
-    } else {
-      for (int c = 0; c < F; ++c) dst[(int64_t)c * kThreads] = 0.0f;
-    }
+    // the stores above and the MLP's per-row loads are one coalesced 128-byte line per warp and channel
+    if (q >= n_samples)
+      for (int c = 0; c < F; ++c) row[(int64_t)c * kThreads] = 0.0f;
     return;
   }
   __syncthreads();
@@ -166,7 +169,7 @@ static int launch_gather(bool from_z, const ucn_frame *f, const float *a, const 
   UCN_CHECK_ARG(f->V >= 1 && f->V <= UCN_MAX_V, "ucn_gather: 1 <= V <= 8 source views");
   if (n <= 0) return UCN_OK;
   const int F = 24 + 12 * f->V + 1;
-  const size_t smem = (size_t)kThreads * (F + 1) * sizeof(float);
+  const size_t smem = tiled ? 0 : (size_t)kThreads * (F + 1) * sizeof(float);
   const unsigned blocks = (unsigned)((n + kThreads - 1) / kThreads);
   if (from_z) {
     static bool attr = false;

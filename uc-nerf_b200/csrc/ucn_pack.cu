@@ -36,6 +36,24 @@ __global__ void pack_cl_kernel(const float *__restrict__ src, float *__restrict_
   }
 }
 
+// feature volume NCDHW [8][D][h][w] -> [h][w][D][8]: depth innermost, so the 126 samples of a ray (which all fall in
+// the same <=4 (x,y) columns of the target-frustum volume, utils/utils.py:852-857) read one contiguous D*32-byte run
+// per column instead of D planes h*w*32 bytes apart.  Block = one image row y x 16 columns x, staged through shared
+// memory so that both the NCDHW reads (along x) and the packed writes (16*D*8 contiguous floats) are coalesced.
+constexpr int kVolTileX = 16;
+__global__ void pack_volume_kernel(const float *__restrict__ src, float *__restrict__ dst, int D, int h, int w) {
+  extern __shared__ float tile[];                       // [kVolTileX][D*8 + 1]
+  const int y = blockIdx.y, x0 = blockIdx.x * kVolTileX, ld = D * 8 + 1;
+  const int nx = min(kVolTileX, w - x0);
+  for (int idx = threadIdx.x; idx < 8 * D * kVolTileX; idx += blockDim.x) {
+    const int x = idx % kVolTileX, z = (idx / kVolTileX) % D, c = idx / (kVolTileX * D);
+    if (x < nx) tile[x * ld + z * 8 + c] = src[(((size_t)c * D + z) * h + y) * w + x0 + x];
+  }
+  __syncthreads();
+  float *out = dst + ((size_t)y * w + x0) * D * 8;
+  for (int e = threadIdx.x; e < nx * D * 8; e += blockDim.x) out[e] = tile[(e / (D * 8)) * ld + e % (D * 8)];
+}
+
 __global__ void pack_nearfar_kernel(const float *__restrict__ dv, float *__restrict__ dst, int D, int hw) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= hw) return;
@@ -92,6 +110,19 @@ extern "C" int ucn_pack_channels_last(const float *src, float *dst, int B, int C
   const int64_t total = (int64_t)B * N;
   pack_cl_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(src, dst, Cn, N, Cpad, total);
   UCN_LAUNCH_CHECK("pack_cl_kernel");
+  return UCN_OK;
+}
+
+extern "C" int ucn_pack_volume(const float *src, float *dst, int D, int h, int w, void *stream) {
+  UCN_CHECK_ARG(src && dst && D > 0 && D <= 256 && h > 0 && w > 0, "ucn_pack_volume: bad argument");
+  const dim3 grid((w + kVolTileX - 1) / kVolTileX, h);
+  const size_t smem = (size_t)kVolTileX * (D * 8 + 1) * sizeof(float);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(pack_volume_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return ucn_cuda_status(e, "pack_volume smem attribute");
+  }
+  pack_volume_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(src, dst, D, h, w);
+  UCN_LAUNCH_CHECK("pack_volume_kernel");
   return UCN_OK;
 }
 

@@ -100,7 +100,7 @@ class PackedFrame:
         return self
 
     def pack_volumes(self, volumes: Sequence):
-        """outputs['stageK']['volume_feature_no_ref'] [1,8,D,h,w] -> [D,h,w,8]."""
+        """outputs['stageK']['volume_feature_no_ref'] [1,8,D,h,w] -> [h,w,D,8] (depth innermost)."""
         lib, st = L.load(), L.stream_ptr()
         for k, vol in enumerate(volumes):
             vol = _dev(vol, self.device)
@@ -111,9 +111,8 @@ class PackedFrame:
             if self.c.D[k] and (self.c.D[k], self.c.h[k], self.c.w[k]) != (D, h, w):
                 raise L.UcnError("volume / depth_values shape mismatch")
             self.c.D[k], self.c.h[k], self.c.w[k] = D, h, w
-            dst = self._alloc(f"vol{k}", D, h, w, 8)
-            L.check(lib.ucn_pack_channels_last(L.ptr(vol.contiguous()), L.ptr(dst), 1, 8, D * h * w, 8, st),
-                    "ucn_pack_channels_last(volume)")
+            dst = self._alloc(f"vol{k}", h, w, D, 8)
+            L.check(lib.ucn_pack_volume(L.ptr(vol.contiguous()), L.ptr(dst), D, h, w, st), "ucn_pack_volume")
             self.c.vol[k] = dst.data_ptr()
         return self
 

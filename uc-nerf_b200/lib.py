@@ -51,6 +51,7 @@ _SIGS = {
     "ucn_launch_count": (C.c_int64, [C.c_int]),
     "ucn_check_device": (C.c_int, []),
     "ucn_pack_channels_last": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int64, C.c_int, _fp]),
+    "ucn_pack_volume": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp]),
     "ucn_pack_nearfar": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp]),
     "ucn_weights_f32_bytes": (C.c_size_t, [C.c_int]),
     "ucn_weights_bf16_bytes": (C.c_size_t, [C.c_int]),
