@@ -23,29 +23,41 @@ constexpr int kThreads = 128;
 
 struct Acc8 { float v[8]; };
 
+// one 8-channel texel = 32 bytes = ONE 256-bit load (LDG.E.256, sm_100): half the load instructions and L1 requests
+// of two float4 loads
+__device__ __forceinline__ void ldg8(const float *__restrict__ p, float4 &lo, float4 &hi) {
+  asm("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+      : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w) : "l"(p));
+}
 __device__ __forceinline__ void fma8(Acc8 &a, const float *__restrict__ texel, float w) {
-  const float4 lo = ucn::ldg4(texel), hi = ucn::ldg4(texel + 4);
+  float4 lo, hi;
+  ldg8(texel, lo, hi);
   a.v[0] = fmaf(lo.x, w, a.v[0]); a.v[1] = fmaf(lo.y, w, a.v[1]);
   a.v[2] = fmaf(lo.z, w, a.v[2]); a.v[3] = fmaf(lo.w, w, a.v[3]);
   a.v[4] = fmaf(hi.x, w, a.v[4]); a.v[5] = fmaf(hi.y, w, a.v[5]);
   a.v[6] = fmaf(hi.z, w, a.v[6]); a.v[7] = fmaf(hi.w, w, a.v[7]);
 }
 
-// trilinear, border padding, align_corners=False, over a [h][w][D][8] volume; channel c -> out[c * os]
+// trilinear, border padding, align_corners=False, over a [h][w][D][8] volume; channel c -> out[c * os].
+// Branch-free: where the reference skips an out-of-range corner (ATen within_bounds test), the corner index is clamped
+// instead and its weight is exactly 0 there (the coordinate was clipped to size-1, so w1 = x - floor(x) = 0): the
+// fma adds +0.  32-bit texel indices (launcher checks every map has < 2^28 texels).
 __device__ __forceinline__ void tri8(const float *__restrict__ vol, int D, int h, int w, float cx, float cy, float cz,
                                      float *__restrict__ out, int os, int32_t *__restrict__ idx) {
   const ucn::Lerp1 ax = ucn::axis(ucn::to_grid(cx), w, false);
   const ucn::Lerp1 ay = ucn::axis(ucn::to_grid(cy), h, false);
   const ucn::Lerp1 az = ucn::axis(ucn::to_grid(cz), D, false);
   if (idx) { idx[0] = ax.i0; idx[1] = ay.i0; idx[2] = az.i0; }
+  const uint32_t x1 = ax.has1 ? 1u : 0u, y1 = ay.has1 ? (uint32_t)w : 0u, z1 = az.has1 ? 1u : 0u;
+  const uint32_t col00 = ((uint32_t)ay.i0 * (uint32_t)w + (uint32_t)ax.i0) * (uint32_t)D + (uint32_t)az.i0;
+  const uint32_t Du = (uint32_t)D;
   Acc8 a = {};
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
     const int dx = c & 1, dy = (c >> 1) & 1, dz = c >> 2;
-    if ((dx && !ax.has1) || (dy && !ay.has1) || (dz && !az.has1)) continue;
     const float wgt = __fmul_rn(__fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0), dz ? az.w1 : az.w0);
-    const size_t t = ((size_t)(ay.i0 + dy) * w + (ax.i0 + dx)) * D + (az.i0 + dz);
-    fma8(a, vol + t * 8, wgt);
+    const uint32_t t = col00 + ((dy ? y1 : 0u) + (dx ? x1 : 0u)) * Du + (dz ? z1 : 0u);
+    fma8(a, vol + (size_t)t * 8, wgt);
   }
 #pragma unroll
   for (int c = 0; c < 8; ++c) out[c * os] = a.v[c];
@@ -68,7 +80,7 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
     const float iw = (float)(f.W - 1), ih = (float)(f.H - 1);
     float p[3], c1[3], c2[3], c3[3];
     if (FROM_Z) {
-      const int r = (int)(q / f.S);
+      const int r = (int)((uint32_t)q / (uint32_t)f.S);         // launcher: n_samples < 2^31
       float ys, xs, d[3], nr[3], fr[3], nx, ny, pz;
       ucn::pixel_of_ray(f, pix_yx, ray0, R, r, ys, xs);
       ucn::ray_dir(f, ys, xs, d);
@@ -106,12 +118,12 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
     {   // confidence: depth-1 "volume" => bilinear, align_corners=False (renderer.py:195, utils.py:859-865)
       const ucn::Lerp1 ax = ucn::axis(ucn::to_grid(c3[0]), f.W, false), ay = ucn::axis(ucn::to_grid(c3[1]), f.H, false);
       float acc = 0.0f;
+      const uint32_t t00 = (uint32_t)ay.i0 * (uint32_t)f.W + (uint32_t)ax.i0;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         const int dx = c & 1, dy = c >> 1;
-        if ((dx && !ax.has1) || (dy && !ay.has1)) continue;
-        acc = fmaf(__ldg(f.conf + (size_t)(ay.i0 + dy) * f.W + ax.i0 + dx),
-                   __fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0), acc);
+        const uint32_t t = t00 + ((dy && ay.has1) ? (uint32_t)f.W : 0u) + ((dx && ax.has1) ? 1u : 0u);
+        acc = fmaf(__ldg(f.conf + t), __fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0), acc);
       }
       row[(F - 1) * os] = acc;
       if (ir) { ir[9] = ax.i0; ir[10] = ay.i0; }
@@ -127,12 +139,12 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
       float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
       Acc8 a = {};
       const float *rgb = f.rgb + (size_t)v * HW * 4, *ft = f.feat + (size_t)v * HW * 8;
+      const uint32_t t00 = (uint32_t)ay.i0 * (uint32_t)f.W + (uint32_t)ax.i0;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const int dx = k & 1, dy = k >> 1;
-        if ((dx && !ax.has1) || (dy && !ay.has1)) continue;
         const float wgt = __fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0);
-        const size_t t = (size_t)(ay.i0 + dy) * f.W + ax.i0 + dx;
+        const size_t t = t00 + ((dy && ay.has1) ? (uint32_t)f.W : 0u) + ((dx && ax.has1) ? 1u : 0u);
         const float4 px = ucn::ldg4(rgb + t * 4);
         c.x = fmaf(px.x, wgt, c.x); c.y = fmaf(px.y, wgt, c.y); c.z = fmaf(px.z, wgt, c.z);
         fma8(a, ft + t * 8, wgt);
@@ -167,6 +179,10 @@ static int launch_gather(bool from_z, const ucn_frame *f, const float *a, const 
                          float *feat, float *ndc_out, int32_t *idx, void *stream) {
   UCN_CHECK_ARG(f && a && feat, "ucn_gather: null argument");
   UCN_CHECK_ARG(f->V >= 1 && f->V <= UCN_MAX_V, "ucn_gather: 1 <= V <= 8 source views");
+  UCN_CHECK_ARG(n < (1ll << 31), "ucn_gather: more than 2^31 samples in one call; split the ray range");
+  for (int k = 0; k < 3; ++k)
+    UCN_CHECK_ARG((long long)f->D[k] * f->h[k] * f->w[k] < (1ll << 28), "ucn_gather: volume has 2^28 texels or more");
+  UCN_CHECK_ARG((long long)f->H * f->W < (1ll << 28), "ucn_gather: image has 2^28 pixels or more");
   if (n <= 0) return UCN_OK;
   const int F = 24 + 12 * f->V + 1;
   const size_t smem = tiled ? 0 : (size_t)kThreads * (F + 1) * sizeof(float);
