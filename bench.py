@@ -36,6 +36,16 @@ FLOP_PER_SAMPLE = lambda V: 2 * (138112 + 1536 * V)          # SURVEY.md §8.0 (
 FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
 
 
+def ncu_traffic(kernel, workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed `ncu --set full` capture
+    (profiles/ncu_traffic.json, written by tools/ncu_traffic.py); None if that kernel/workload was not captured."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        return json.load(open(p)).get(workload, {}).get(kernel)
+    except (OSError, ValueError):
+        return None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -86,6 +96,19 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def cpu_sample_rays(O, osc, ow, H, W, S, target_s, row0):
+    """Rays for a CPU sample of about `target_s` seconds: probe with 2048 rays, scale, clamp to the frame
+    (whole image rows starting at `row0`, so the sample is a contiguous band of the same frame)."""
+    probe = 2048
+    tr = np.random.default_rng(1).random((probe, S), dtype=np.float32)
+    O.render_rays(osc, ow, row0, 256, tr[:256])                       # page in / spin up the thread pool
+    t0 = time.perf_counter()
+    O.render_rays(osc, ow, row0, probe, tr)
+    rate = probe / (time.perf_counter() - t0)
+    n = int(rate * target_s) // W * W
+    return max(W, min(n, H * W - row0))
+
+
 def run_reference(args, wl):
     """CPU arm: the oracle port of the reference's path on all host cores, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
@@ -97,9 +120,9 @@ def run_reference(args, wl):
     sc = synthetic.make_scene(H, W, V, seed=0)
     wts = synthetic.make_weights(V, seed=0)
     osc, ow = O.OracleScene(sc, S, dir_switch=1024), O.OracleWeights(wts, V)
-    n = args.cpu_rays
+    row0 = (H // 4) * W
+    n = args.cpu_rays or cpu_sample_rays(O, osc, ow, H, W, S, 5.0, row0)    # ~5 s per step
     t_rand = np.random.default_rng(0).random((n, S), dtype=np.float32)
-    row0 = (H // 2) * W
     for _ in range(args.warmup):
         O.render_rays(osc, ow, row0, min(n, 512), t_rand[:min(n, 512)])
     t0 = time.perf_counter()
@@ -107,7 +130,8 @@ def run_reference(args, wl):
         O.render_rays(osc, ow, row0, n, t_rand)
     dt = (time.perf_counter() - t0) / args.steps
     v = n / dt
-    sample = f"{n} rays (rows from the image centre) of the {H}x{W} frame per step, S={S}, V'={V}"
+    sample = (f"{n} rays ({n // W} image rows from row {row0 // W}) of the {H}x{W} frame per step ({dt:.1f} s), S={S}, "
+              f"V'={V}, OpenMP on {O.num_threads()} threads")
     print(json.dumps({
         "impl": "reference", "metric": "rays/sec", "value": v, "unit": "rays/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
@@ -127,7 +151,7 @@ def main():
     ap.add_argument("--mode", default=os.environ.get("UCNERF_BENCH_MODE", "bf16"), choices=["bf16", "bf16_fast", "fp32"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--max-rays", type=int, default=0, help="rays per launch group (0 = auto)")
-    ap.add_argument("--cpu-rays", type=int, default=8192, help="bounded CPU sample (rays) for the baseline")
+    ap.add_argument("--cpu-rays", type=int, default=0, help="bounded CPU sample (rays); 0 = sized for ~15 s (ours) / ~5 s per step (reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
@@ -159,9 +183,6 @@ def main():
             "conf": torch.from_numpy(sc.confidence).pin_memory()}
     h2d_bytes = sum(t.numel() * 4 for t in host["dv"] + host["vol"] + [host["feat"], host["imgs"], host["conf"]])
     resident = {k: ([t.to(dev) for t in v] if isinstance(v, list) else v.to(dev)) for k, v in host.items()}
-    staging = {k: ([torch.empty_like(t) for t in v] if isinstance(v, list) else torch.empty_like(v))
-               for k, v in resident.items()}
-    out_host = torch.empty((n_rays, 4), dtype=torch.float32).pin_memory()
     max_rays = args.max_rays or n_rays
 
     def pack(maps):
@@ -184,20 +205,12 @@ def main():
         ren.frame = fr
         ren.render(seed=seed, out_rgb=rgb, out_depth=depth, timers=timers)
 
-    def step_e2e(seed):
-        for k, v in host.items():
-            if isinstance(v, list):
-                for s, d in zip(v, staging[k]):
-                    d.copy_(s, non_blocking=True)
-            else:
-                staging[k].copy_(v, non_blocking=True)
-        fr = pack(staging)
-        ren = ren_box["r"]
-        ren.frame = fr
-        ren.render(seed=seed, out_rgb=rgb, out_depth=depth, timers=None)
-        out_host[:, :3].copy_(rgb, non_blocking=True)
-        out_host[:, 3].copy_(depth, non_blocking=True)
-        torch.cuda.current_stream().synchronize()       # the caller reads the image: that is the API contract
+    from ucnerf_b200.frame import HostSweep
+    sweep = HostSweep(pw, pack, n_rays, args.mode, dev)
+
+    def step_e2e(i, last):
+        # view i from pinned host maps -> pinned host image; view i+1's maps cross PCIe while view i renders
+        sweep.render(i, host, None if last else host, seed=i)
 
     def barrier():
         if world > 1:
@@ -221,8 +234,8 @@ def main():
 
     for i in range(args.warmup):
         step_resident({}, 1000 + i)
-    for i in range(max(1, args.warmup // 2)):
-        step_e2e(2000 + i)
+    for i in range(max(2, args.warmup // 2)):
+        step_e2e(i, i + 1 == max(2, args.warmup // 2))
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -231,7 +244,7 @@ def main():
     ms, wall_ms = timed(lambda i: step_resident(timers, i), args.steps)
     launches = L.launch_count() // args.steps
     clocks = sampler.stop() if rank == 0 else None
-    e2e_ms, e2e_wall = timed(lambda i: step_e2e(i), args.steps)
+    e2e_ms, e2e_wall = timed(lambda i: step_e2e(i, i + 1 == args.steps), args.steps)
     e2e_ms = max(e2e_ms, e2e_wall)                       # host work is part of the end-to-end call
 
     kern = {k: sum(a.elapsed_time(b) for a, b in v) / args.steps for k, v in timers.items()}   # ms per step
@@ -263,10 +276,12 @@ def main():
             "clocks": clocks,
             "roofline": {"kernel": {"bf16": "mlp_x3_kernel", "bf16_fast": "mlp_tc_kernel", "fp32": "mlp_fp32_kernel"}[args.mode], "bound": "tensor",
                          "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
-                         "traffic": None, "peak_source": pk["_source"] + " (bf16_tflops_sustained)",
+                         "traffic": ncu_traffic({"bf16": "mlp_x3_kernel", "bf16_fast": "mlp_tc_kernel", "fp32": "mlp_fp32_kernel"}[args.mode], args.workload),
+                         "peak_source": pk["_source"] + " (bf16_tflops_sustained)",
                          "flops_per_launch": flops_per_launch, "ms_per_launch": mlp_ms_per_launch},
             "kernels_ms_per_step": kern,
             "hbm_kernels": {"gather_GBps": gather_gbs, "gather_frac": gather_gbs / pk["hbm_gbs"],
+                            "gather_traffic": ncu_traffic("gather_kernel", args.workload),
                             "composite_GBps": comp_gbs, "composite_frac": comp_gbs / pk["hbm_gbs"],
                             "peak_GBps": pk["hbm_gbs"]},
             "wall_ms_per_step": wall_ms,
@@ -274,15 +289,14 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             from oracle import oracle as O
             osc, ow = O.OracleScene(sc, S, dir_switch=1024), O.OracleWeights(wts, V)
-            n = args.cpu_rays
+            row0 = (H // 4) * W
+            n = args.cpu_rays or cpu_sample_rays(O, osc, ow, H, W, S, 15.0, row0)
             tr = np.random.default_rng(0).random((n, S), dtype=np.float32)
-            row0 = (H // 2) * W
-            O.render_rays(osc, ow, row0, 256, tr[:256])
             t0 = time.perf_counter()
             rgb_o, _ = O.render_rays(osc, ow, row0, n, tr)
             dt = time.perf_counter() - t0
             line["cpu_baseline"] = {"value": n / dt, "unit": "rays/s", "cores": O.num_threads(), "kind": "port",
-                                    "sample": f"{n} rays from the centre rows of the same {H}x{W} frame ({dt:.1f} s)"}
+                                    "sample": f"{n} rays ({n // W} image rows from row {row0 // W}) of the same {H}x{W} frame ({dt:.1f} s)"}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -272,3 +272,67 @@ def render_frame(frame: PackedFrame, weights: PackedWeights, mode: str = "bf16",
                  ray0: int = 0, n_rays: Optional[int] = None, max_rays: Optional[int] = None):
     """One call per target view: (rgb [R,3], depth [R]) for rays ray0..ray0+R of the row-major pixel grid."""
     return FrameRenderer(frame, weights, mode, max_rays).render(ray0, n_rays, t_rand, seed)
+
+
+class HostSweep:
+    """Novel-view sweep from HOST maps (BASELINE config 3 shape: one set of encoder outputs per target view).
+
+    ``render(i, host_maps, next_host_maps)`` renders view i from pinned host tensors and returns the image in a
+    pinned host buffer.  The maps of view i+1 are copied host->device on a side stream while view i renders
+    (two staging sets), so the PCIe transfer of every view is inside the sweep but off its critical path; the
+    result is copied device->host and the call synchronises, as the reference's eval loop does per chunk
+    (train.py:274-275).  `make_frame(dev_maps)` builds the PackedFrame (cameras + ucn_pack_* of the staged maps).
+    """
+
+    def __init__(self, weights: PackedWeights, make_frame, n_rays: int, mode: str = "bf16", device="cuda"):
+        self.device = torch.device(device)
+        self.weights, self.make_frame, self.mode, self.n_rays = weights, make_frame, mode, int(n_rays)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.staging = [None, None]
+        self.copied = [torch.cuda.Event(), torch.cuda.Event()]
+        self.free = [torch.cuda.Event(), torch.cuda.Event()]
+        self.pending = [None, None]                     # id of the host map set staged (or in flight) per slot
+        self.renderer: Optional[FrameRenderer] = None
+        self.rgb = torch.empty((self.n_rays, 3), device=self.device)
+        self.depth = torch.empty((self.n_rays,), device=self.device)
+        self.out_host = torch.empty((self.n_rays, 4), dtype=torch.float32).pin_memory()
+        for e in self.free:
+            e.record(torch.cuda.current_stream(self.device))
+
+    @staticmethod
+    def _walk(maps):
+        for k, v in maps.items():
+            for j, t in enumerate(v if isinstance(v, (list, tuple)) else [v]):
+                yield k, j, t
+
+    def _enqueue(self, slot, host_maps, tag):
+        if self.staging[slot] is None:
+            self.staging[slot] = {k: ([torch.empty(t.shape, device=self.device) for t in v] if isinstance(v, (list, tuple))
+                                      else torch.empty(v.shape, device=self.device)) for k, v in host_maps.items()}
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.free[slot])            # the previous user of this staging set is done
+            for k, j, t in self._walk(host_maps):
+                dst = self.staging[slot][k]
+                (dst[j] if isinstance(dst, list) else dst).copy_(t, non_blocking=True)
+            self.copied[slot].record(self.copy_stream)
+        self.pending[slot] = tag
+
+    def render(self, i: int, host_maps, next_host_maps=None, seed: int = 0):
+        slot = i & 1
+        main = torch.cuda.current_stream(self.device)
+        if self.pending[slot] != i:
+            self._enqueue(slot, host_maps, i)
+        if next_host_maps is not None:
+            self._enqueue(slot ^ 1, next_host_maps, i + 1)          # overlaps this view's kernels
+        main.wait_event(self.copied[slot])
+        fr = self.make_frame(self.staging[slot])
+        if self.renderer is None:
+            self.renderer = FrameRenderer(fr, self.weights, self.mode, max_rays=self.n_rays)
+        self.renderer.frame = fr
+        self.renderer.render(seed=seed, out_rgb=self.rgb, out_depth=self.depth)
+        self.free[slot].record(main)
+        self.out_host[:, :3].copy_(self.rgb, non_blocking=True)
+        self.out_host[:, 3].copy_(self.depth, non_blocking=True)
+        main.synchronize()                                          # the caller reads the image
+        self.pending[slot] = None
+        return self.out_host
