@@ -120,6 +120,7 @@ def run_reference(args, wl):
     sc = synthetic.make_scene(H, W, V, seed=0)
     wts = synthetic.make_weights(V, seed=0)
     osc, ow = O.OracleScene(sc, S, dir_switch=1024), O.OracleWeights(wts, V)
+    O.set_num_threads(os.cpu_count())                 # torchrun exports OMP_NUM_THREADS=1 to its ranks
     row0 = (H // 4) * W
     n = args.cpu_rays or cpu_sample_rays(O, osc, ow, H, W, S, 5.0, row0)    # ~5 s per step
     t_rand = np.random.default_rng(0).random((n, S), dtype=np.float32)
@@ -289,6 +290,7 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             from oracle import oracle as O
             osc, ow = O.OracleScene(sc, S, dir_switch=1024), O.OracleWeights(wts, V)
+            O.set_num_threads(os.cpu_count())
             row0 = (H // 4) * W
             n = args.cpu_rays or cpu_sample_rays(O, osc, ow, H, W, S, 15.0, row0)
             tr = np.random.default_rng(0).random((n, S), dtype=np.float32)

@@ -43,7 +43,9 @@ class _Weights(C.Structure):
 
 def build(force: bool = False) -> str:
     """Compile the oracle with the committed Makefile (gcc only; no reference sources involved)."""
-    if force or not os.path.exists(_LIB_PATH):
+    srcs = [os.path.join(_HERE, f) for f in ("ucnerf_oracle.c", "ucnerf_oracle_mlp.c", "ucnerf_oracle.h", "Makefile")]
+    stale = os.path.exists(_LIB_PATH) and any(os.path.getmtime(f) > os.path.getmtime(_LIB_PATH) for f in srcs)
+    if force or stale or not os.path.exists(_LIB_PATH):
         subprocess.run(["make", "-C", _HERE, "-s"], check=True)
     return _LIB_PATH
 
@@ -227,3 +229,9 @@ def render_rays(osc: OracleScene, ow: OracleWeights, ray0: int, R: int, t_rand):
 
 def num_threads() -> int:
     return int(lib().uco_num_threads())
+
+
+def set_num_threads(n: int) -> int:
+    """OpenMP threads of the oracle (torchrun exports OMP_NUM_THREADS=1; the timed CPU legs want every core)."""
+    lib().uco_set_num_threads(int(n))
+    return num_threads()

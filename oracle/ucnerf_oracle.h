@@ -52,4 +52,5 @@ void uco_mlp(const uco_weights *wt, const float *ndc_pts, const float *feat, con
 void uco_render_rays(const uco_scene *sc, const uco_weights *wt, int ray0, int R, const float *t_vals,
                      const float *t_rand, float *rgb, float *depth);
 int uco_num_threads(void);
+void uco_set_num_threads(int n);
 #endif

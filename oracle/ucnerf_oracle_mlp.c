@@ -18,6 +18,15 @@
 
 #define BLK 48
 
+/* torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU baseline legs ask for all host cores explicitly. */
+void uco_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int uco_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();
