@@ -133,6 +133,12 @@ int ucn_raygen_sample(const ucn_frame *f, const float *pix_yx, int ray0, int R, 
                       const float *t_rand, uint64_t seed, float *z, float *rays_d, float *pts, float *ndc,
                       void *stream);
 
+/* data/ray_utils.py:152-197 ray_marcher (not on the live eval path; kept as a thin mode of K1):
+ * rays [R][8] = (origin, direction, near, far); t_vals = linspace(0,1,S); t_rand [R][S] uniforms (needed when
+ * perturb > 0).  Outputs xyz [R][S][3], z [R][S]. */
+int ucn_ray_marcher(const float *rays, int R, int S, const float *t_vals, const float *t_rand, float perturb,
+                    int lindisp, float *xyz, float *z, void *stream);
+
 /* ---- K2: projection + fused gathers -> feature rows ----------------------------------------
  * replaces index_point_feature (utils/utils.py:833-893), build_color_volume (:742-799),
  * get_ndc_coordinate(sample_2d=True) (:323-347) and gen_pts_feats (network/renderer.py:177-212).

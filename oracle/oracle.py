@@ -227,6 +227,16 @@ def render_rays(osc: OracleScene, ow: OracleWeights, ray0: int, R: int, t_rand):
     return rgb, depth
 
 
+def ray_marcher(rays: np.ndarray, S: int, lindisp: bool = False, perturb: float = 0.0, rnd: Optional[np.ndarray] = None):
+    """data/ray_utils.py:152-197 -> (xyz [R,S,3], z [R,S])."""
+    rays = _f32(rays)
+    R = rays.shape[0]
+    xyz, z = np.empty((R, S, 3), np.float32), np.empty((R, S), np.float32)
+    rnd = _f32(rnd) if rnd is not None else None
+    lib().uco_ray_marcher(_p(rays), R, S, _p(linspace01(S)), _p(rnd), C.c_float(perturb), int(lindisp), _p(xyz), _p(z))
+    return xyz, z
+
+
 def num_threads() -> int:
     return int(lib().uco_num_threads())
 

@@ -247,3 +247,33 @@ void uco_composite(const float *raw, const float *z, int R, int S, float *rgb, f
     depth[r] = dm;
   }
 }
+
+/* data/ray_utils.py:152-197 ray_marcher.  rays [R][8] = (o, d, near, far); t = linspace(0,1,S); rnd [R][S] uniforms
+ * (used when perturb > 0).  xyz [R][S][3], z [R][S].  Every elementwise op of the reference rounds on its own. */
+static inline float marcher_z(float near, float far, float t, int lindisp) {
+  const float omt = 1.0f - t;
+  if (!lindisp) { const float a = near * omt, b = far * t; return a + b; }
+  const float in = 1.0f / near, jf = 1.0f / far;
+  const float a = in * omt, b = jf * t;
+  const float s = a + b;
+  return 1.0f / s;
+}
+void uco_ray_marcher(const float *rays, int R, int S, const float *t, const float *rnd, float perturb, int lindisp,
+                     float *xyz, float *z) {
+  for (int r = 0; r < R; ++r) {
+    const float *ray = rays + (size_t)r * 8;
+    for (int j = 0; j < S; ++j) {
+      float zj = marcher_z(ray[6], ray[7], t[j], lindisp);
+      if (perturb > 0.0f) {
+        float lower = zj, upper = zj;
+        if (j > 0) { const float sm = marcher_z(ray[6], ray[7], t[j - 1], lindisp) + zj; lower = 0.5f * sm; }
+        if (j < S - 1) { const float sm = zj + marcher_z(ray[6], ray[7], t[j + 1], lindisp); upper = 0.5f * sm; }
+        const float w = upper - lower, pr = perturb * rnd[(size_t)r * S + j];
+        const float wp = w * pr;
+        zj = lower + wp;
+      }
+      z[(size_t)r * S + j] = zj;
+      for (int c = 0; c < 3; ++c) { const float dz = ray[3 + c] * zj; xyz[((size_t)r * S + j) * 3 + c] = ray[c] + dz; }
+    }
+  }
+}

@@ -51,6 +51,8 @@ void uco_mlp(const uco_weights *wt, const float *ndc_pts, const float *feat, con
 /* whole path for n rays starting at global ray index ray0 of the row-major pixel grid */
 void uco_render_rays(const uco_scene *sc, const uco_weights *wt, int ray0, int R, const float *t_vals,
                      const float *t_rand, float *rgb, float *depth);
+void uco_ray_marcher(const float *rays, int R, int S, const float *t, const float *rnd, float perturb, int lindisp,
+                     float *xyz, float *z);
 int uco_num_threads(void);
 void uco_set_num_threads(int n);
 #endif

@@ -297,3 +297,19 @@ def test_config1_size_properties():
             assert np.abs(rgb[ray0:ray0 + 256].cpu().numpy() - rgb_o).max() <= tol, mode
             if mode == "fp32":
                 assert np.abs(depth[ray0:ray0 + 256].cpu().numpy() - depth_o).max() <= 1e-4
+
+
+@pytest.mark.parametrize("name", ("lin", "lin_jit", "disp_jit"))
+def test_ray_marcher_bit_exact(name, golden_dir):
+    """ucn_ray_marcher (data/ray_utils.py:152-197) vs the oracle and the reference-generated golden, bit for bit."""
+    import sys
+    sys.path.insert(0, golden_dir)
+    from make_golden_marcher import marcher_inputs
+    from ucnerf_b200 import rays as R
+    g = np.load(f"{golden_dir}/ray_marcher.npz")
+    rays, rnd, c = marcher_inputs(name)
+    xyz, o, d, z = R.ray_marcher(T(rays), N_samples=c["S"], lindisp=c["lindisp"], perturb=c["perturb"], t_rand=T(rnd))
+    xyz_o, z_o = O.ray_marcher(rays, c["S"], c["lindisp"], c["perturb"], rnd)
+    assert np.array_equal(bits(z.cpu().numpy()), bits(z_o)) and np.array_equal(bits(z_o), bits(g[name + "_z"]))
+    assert np.array_equal(bits(xyz.cpu().numpy()), bits(xyz_o)) and np.array_equal(bits(xyz_o), bits(g[name + "_xyz"]))
+    assert np.array_equal(o.cpu().numpy(), rays[:, 0:3]) and np.array_equal(d.cpu().numpy(), rays[:, 3:6])

@@ -65,3 +65,16 @@ def test_embed_order():
     assert np.allclose(e[3:6], np.sin(x[0]))           # [x | all sin | all cos], Q6
     assert np.allclose(e[6:9], np.sin(2 * x[0]))
     assert np.allclose(e[15:18], np.cos(x[0]))
+
+
+@pytest.mark.parametrize("name", ("lin", "lin_jit", "disp_jit"))
+def test_ray_marcher_bit_exact(name, golden_dir):
+    """data/ray_utils.py:152-197 restated in oracle/ucnerf_oracle.c vs the reference's own output."""
+    import sys
+    sys.path.insert(0, golden_dir)
+    from make_golden_marcher import marcher_inputs
+    g = np.load(f"{golden_dir}/ray_marcher.npz")
+    rays, rnd, c = marcher_inputs(name)
+    xyz, z = O.ray_marcher(rays, c["S"], c["lindisp"], c["perturb"], rnd)
+    assert np.array_equal(bits(z), bits(g[name + "_z"]))
+    assert np.array_equal(bits(xyz), bits(g[name + "_xyz"]))

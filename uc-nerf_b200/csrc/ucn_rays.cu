@@ -124,7 +124,47 @@ __global__ void dir_feature_kernel(const __grid_constant__ ucn_frame f, const fl
   angle[3 * r] = a[0]; angle[3 * r + 1] = a[1]; angle[3 * r + 2] = a[2];
 }
 
+// data/ray_utils.py:152-197 ray_marcher: uniform (or disparity-uniform) samples between per-ray near/far, optional
+// stratified jitter, world points.  One thread per (ray, sample); every product and sum rounds on its own, as the
+// reference's separate elementwise kernels do.
+__device__ __forceinline__ float marcher_z(float near, float far, float t, int lindisp) {
+  const float omt = __fsub_rn(1.0f, t);
+  if (!lindisp) return __fadd_rn(__fmul_rn(near, omt), __fmul_rn(far, t));
+  return __fdiv_rn(1.0f, __fadd_rn(__fmul_rn(__fdiv_rn(1.0f, near), omt), __fmul_rn(__fdiv_rn(1.0f, far), t)));
+}
+__global__ void ray_marcher_kernel(const float *__restrict__ rays, int R, int S, const float *__restrict__ t_vals,
+                                   const float *__restrict__ t_rand, float perturb, int lindisp,
+                                   float *__restrict__ xyz, float *__restrict__ z_out) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= (int64_t)R * S) return;
+  const int r = (int)(q / S), j = (int)(q - (int64_t)r * S);
+  const float *ray = rays + (size_t)r * 8;
+  const float near = ray[6], far = ray[7];
+  float z = marcher_z(near, far, t_vals[j], lindisp);
+  if (perturb > 0.0f) {
+    const float lower = j == 0 ? z : __fmul_rn(0.5f, __fadd_rn(marcher_z(near, far, t_vals[j - 1], lindisp), z));
+    const float upper = j == S - 1 ? z : __fmul_rn(0.5f, __fadd_rn(z, marcher_z(near, far, t_vals[j + 1], lindisp)));
+    z = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), __fmul_rn(perturb, t_rand[q])));
+  }
+  z_out[q] = z;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) xyz[3 * q + c] = __fadd_rn(ray[c], __fmul_rn(ray[3 + c], z));
+}
+
 }  // namespace
+
+extern "C" int ucn_ray_marcher(const float *rays, int R, int S, const float *t_vals, const float *t_rand, float perturb,
+                               int lindisp, float *xyz, float *z, void *stream) {
+  UCN_CHECK_ARG(rays && t_vals && xyz && z, "ucn_ray_marcher: null argument");
+  UCN_CHECK_ARG(S > 0 && R >= 0, "ucn_ray_marcher: bad sizes");
+  UCN_CHECK_ARG(!(perturb > 0.0f) || t_rand, "ucn_ray_marcher: perturb > 0 needs t_rand");
+  if (R == 0) return UCN_OK;
+  const int64_t n = (int64_t)R * S;
+  ray_marcher_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(rays, R, S, t_vals, t_rand, perturb,
+                                                                                    lindisp, xyz, z);
+  UCN_LAUNCH_CHECK("ray_marcher_kernel");
+  return UCN_OK;
+}
 
 extern "C" int ucn_raygen_sample(const ucn_frame *f, const float *pix_yx, int ray0, int R, const float *t_vals,
                                  const float *t_rand, uint64_t seed, float *z, float *rays_d, float *pts,

@@ -59,6 +59,7 @@ _SIGS = {
     "ucn_pack_weights": (C.c_int, [C.POINTER(StateDict), _fp, _fp, _fp, _fp]),
     "ucn_raygen_sample": (C.c_int, [C.POINTER(Frame), _fp, C.c_int, C.c_int, _fp, _fp, C.c_uint64, _fp, _fp, _fp,
                                     _fp, _fp]),
+    "ucn_ray_marcher": (C.c_int, [_fp, C.c_int, C.c_int, _fp, _fp, C.c_float, C.c_int, _fp, _fp, _fp]),
     "ucn_gather": (C.c_int, [C.POINTER(Frame), _fp, _fp, _fp, _fp, C.c_int64, C.c_int, _fp, _fp, _fp]),
     "ucn_project_points": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_int, C.c_int, _fp, C.c_int64,
                                      _fp, _fp]),

@@ -6,6 +6,7 @@ Same names, argument order, return tuples and tensor shapes as the reference fun
     utils/utils.py:323   get_ndc_coordinate      utils/utils.py:393   sample_points_uniform
     utils/utils.py:742   build_color_volume      utils/utils.py:833   index_point_feature
     data/ray_utils.py:12 get_ray_directions      data/ray_utils.py:32 get_rays
+    data/ray_utils.py:152 ray_marcher
 
 Everything runs on the tensors' CUDA device; there is no CPU path (``use_cpu=True`` raises).
 """
@@ -139,6 +140,23 @@ def get_rays(directions, c2w):
     rays_d = directions.reshape(-1, 3) @ c2w[:3, :3].T
     rays_o = c2w[:3, 3].expand(rays_d.shape)
     return rays_o, rays_d
+
+
+def ray_marcher(rays, N_samples=64, lindisp=False, perturb=0, bbox_3D=None, t_rand: Optional[torch.Tensor] = None):
+    """data/ray_utils.py:152-197.  rays [N,8] = (o, d, near, far) -> (xyz [N,S,3], rays_o, rays_d, z_vals [N,S]).
+    ``t_rand`` ([N,S] uniforms) replaces the reference's internal ``torch.rand`` when perturb > 0."""
+    _need_cuda(rays, "ray_marcher")
+    rays = rays.to(torch.float32).contiguous()
+    R, S = rays.shape[0], int(N_samples)
+    xyz = torch.empty((R, S, 3), device=rays.device)
+    z = torch.empty((R, S), device=rays.device)
+    if perturb > 0 and t_rand is None:
+        t_rand = torch.rand((R, S), device=rays.device)
+    if t_rand is not None:
+        t_rand = t_rand.to(device=rays.device, dtype=torch.float32).contiguous()
+    L.check(L.load().ucn_ray_marcher(L.ptr(rays), R, S, L.ptr(linspace01(S, rays.device)), L.ptr(t_rand), float(perturb),
+                                     int(bool(lindisp)), L.ptr(xyz), L.ptr(z), L.stream_ptr()), "ucn_ray_marcher")
+    return xyz, rays[:, 0:3], rays[:, 3:6], z
 
 
 def get_ndc_coordinate(w2c_ref, intrinsic_ref, point_samples, inv_scale, near_far=None, sample_2d=False):
