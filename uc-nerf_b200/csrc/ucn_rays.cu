@@ -47,17 +47,53 @@ raygen_sample_kernel(const __grid_constant__ ucn_frame f, const float *__restric
   ucn::stage_near_far(f, ys, xs, nr, fr);
 
   // three uniform sweeps, near*(1-t) + far*t with separate roundings (utils/utils.py:396)
+  auto sweep = [&](int k, int j) {           // (selects, not indexing: nr/fr stay in registers)
+    const float t = __ldg(t_vals + j);
+    const float nk = k == 0 ? nr[0] : (k == 1 ? nr[1] : nr[2]), fk = k == 0 ? fr[0] : (k == 1 ? fr[1] : fr[2]);
+    return __fadd_rn(__fmul_rn(nk, __fsub_rn(1.0f, t)), __fmul_rn(fk, t));
+  };
+  // torch.sort of their concatenation (utils/utils.py:698-700), values only.  Each sweep is non-decreasing (checked
+  // below), so the sorted position of element j of sweep k is j + the number of smaller elements in the other two
+  // sweeps: two 6-step binary searches per element instead of a 28-stage bitonic network.  Ties between sweeps are
+  // broken by sweep index (<= against earlier sweeps, < against later ones), which makes the ranks a permutation;
+  // equal values are interchangeable in a value-only sort.
+  bool monotone = true;
+  for (int i = lane; i < S; i += 32) {
+    const int k = i / n, j = i - k * n;
+    if (j + 1 < n) monotone = monotone && (sweep(k, j) <= sweep(k, j + 1));
+  }
+  if (__all_sync(0xffffffffu, monotone)) {
+    for (int i = lane; i < S; i += 32) {
+      const int k = i / n, j = i - k * n;
+      const float v = sweep(k, j);
+      int rank = j;
+#pragma unroll
+      for (int m = 0; m < 3; ++m) {
+        if (m == k) continue;
+        // number of elements of sweep m that sort before v: first index with sweep(m, idx) > v (m < k) or >= v (m > k)
+        int lo = 0, hi = n;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          const float w = sweep(m, mid);
+          const bool before = m < k ? (w <= v) : (w < v);
+          if (before) lo = mid + 1; else hi = mid;
+        }
+        rank += lo;
+      }
+      zs[rank] = v;
+    }
+    __syncwarp();
+  } else {
+  // degenerate sweeps (never seen with near < far; kept for exactness): bitonic sort of P (power of two) values
   for (int i = lane; i < P; i += 32) {
     float v = __int_as_float(0x7f800000);   // +inf padding sorts to the end
     if (i < S) {
       const int k = i / n, j = i - k * n;
-      const float t = __ldg(t_vals + j);
-      v = __fadd_rn(__fmul_rn(nr[k], __fsub_rn(1.0f, t)), __fmul_rn(fr[k], t));
+      v = sweep(k, j);
     }
     zs[i] = v;
   }
   __syncwarp();
-  // bitonic sort of P (power of two) values by one warp: value-only sort == torch.sort values
   for (int k2 = 2; k2 <= P; k2 <<= 1) {
     for (int j = k2 >> 1; j > 0; j >>= 1) {
       for (int i = lane; i < P; i += 32) {
@@ -70,6 +106,7 @@ raygen_sample_kernel(const __grid_constant__ ucn_frame f, const float *__restric
       }
       __syncwarp();
     }
+  }
   }
 
   if (rays_d_out && lane < 3) rays_d_out[(size_t)r * 3 + lane] = d[lane];
