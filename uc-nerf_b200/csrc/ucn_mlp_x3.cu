@@ -175,6 +175,14 @@ __device__ __forceinline__ void pos_enc(const float (&x)[3], float *pe) {
 }
 
 
+// "touch" load: pulls a line into L1/L2 ahead of its real use (result discarded).  Plain loads issued while the MMAs
+// saturate shared memory take 3-4 K cycles to come back (trace: tools/trace_x3.py), so every global input of an
+// epilogue is touched one round early, by warps that are idle then.
+__device__ __forceinline__ void touch(const float *p) {
+  float t;
+  asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(t) : "l"(p));
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict__ wpack, int V,
               const float *__restrict__ ndc_pts, const float *__restrict__ feat, long long f_tile_stride,
@@ -352,6 +360,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
 #pragma unroll
         for (int c = 0; c < 8; ++c) store_chunk_x3(h_row, c, pe + 8 * c);
         u = 1.0f - (valid ? __ldg(frow + (F - 1) * f_k_stride) : 0.0f);          // models.py:149
+        tr.ev(6, 6, g);
       } else {
         // all loads of a 32-channel group are issued before the first use: one memory round trip per group
 #pragma unroll 1
@@ -365,6 +374,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             if (g4 + c < L.Kfilm / 8) store_chunk_x3(h_row, 8 + g4 + c, v + 8 * c);
+          tr.ev(6, 7, g);
         }
       }
       arrive_in();
@@ -386,16 +396,32 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
             pe[63] = 0.0f;
 #pragma unroll
             for (int c = 0; c < 8; ++c) store_chunk_x3(h_row, c, pe + 8 * c);
+          } else {
+            // warpgroup 1 is idle in this round: it touches the [img feats] lines round 6 will read, and computes the
+            // per-ray view-direction term of views|view_confi (column `row`) for every ray of the tile (read in round 9)
+            if (valid)
+              for (int k = 0; k < Kfb_real; ++k) touch(frow + (Kfilm_real + k) * f_k_stride);
+            for (int i = 0; i < nrays_tile; ++i) {
+              const uint32_t ray = ray_first + i;
+              const float a[3] = {__ldg(angle + 3 * ray), __ldg(angle + 3 * ray + 1), __ldg(angle + 3 * ray + 2)};
+              float pe[27];
+              pos_enc<4>(a, pe);
+              float acc = 0.f;
+#pragma unroll
+              for (int k = 0; k < 27; ++k) acc = fmaf(__ldg(f32g + ucn::X3Layout::vd + k * 128 + row), pe[k], acc);
+              rayb_s[(s * rpt + i) * 128 + row] = acc;
+            }
           }
         } else if (r == 6) {
           head[0] = head[1] = head[2] = head[3] = 0.f;
           epi64<0, true>(t_acc, t_mod, col0, bias_s + 128 * 5, nullptr, h_row, f32s + ucn::X3Layout::w_base, head);
+          tr.ev(6, 1, g);
           if (hf == 1) {
             exch_s[s * 128 + row] = make_float4(head[0], head[1], head[2], head[3]);
             named_bar_arrive(bar_id, 256);
             // [img feats | 1] as split bf16 pairs -> TMEM acc columns 64.. (hi) and 96.. (lo): A operand of fb
 #pragma unroll 1
-            for (int h16 = 0; h16 < 2; ++h16) {
+            for (int h16 = 0; h16 < (L.Kfb + 31) / 32; ++h16) {     // 32 K values (16 hi + 16 lo words) per pass
               uint32_t hi[16], lo[16];
 #pragma unroll
               for (int j = 0; j < 16; ++j) {
@@ -405,6 +431,7 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
                 if (k + 1 < Kfb_real) b = valid ? __ldg(frow + (Kfilm_real + k + 1) * f_k_stride) : 0.f; else if (k + 1 == Kfb_real) b = 1.f;
                 split2(a, b, hi[j], lo[j]);
               }
+              tr.ev(6, 2, g);
               tmem_st16(t_acc + 64 + 16 * h16, hi);
               tmem_st16(t_acc + 96 + 16 * h16, lo);
             }
@@ -418,24 +445,24 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
           }
         } else if (r == 7) {
           epi64<3, false>(t_acc, t_mod, col0, nullptr, nullptr, h_row, nullptr, head);
+          {
+            // touch the next tile's inputs (position, confidence, film channels: half per warpgroup)
+            const long long nt = tile + 2ll * gridDim.x;
+            const uint32_t nq = (uint32_t)nt * 128u + row;
+            if (nt < ntiles && nq < Nu) {
+              const float *nrow = feat + nt * f_tile_stride + (long long)row * f_row_stride;
+              if (hf == 0) { touch(ndc_pts + 3 * nq); touch(ndc_pts + 3 * nq + 2); touch(nrow + (F - 1) * f_k_stride); }
+              for (int k = hf; k < Kfilm_real; k += 2) touch(nrow + k * f_k_stride);
+            }
+          }
         } else if (r == 8) {
           epi64<1, false>(t_acc, t_mod, col0, f32s + ucn::X3Layout::b_feat, nullptr, h_row, nullptr, head);
-          // per-ray view-direction term of views|view_confi: column `row`, rays hf, hf+2, ... of this tile
-          for (int i = hf; i < nrays_tile; i += 2) {
-            const uint32_t ray = ray_first + i;
-            const float a[3] = {__ldg(angle + 3 * ray), __ldg(angle + 3 * ray + 1), __ldg(angle + 3 * ray + 2)};
-            float pe[27];
-            pos_enc<4>(a, pe);
-            float acc = 0.f;
-#pragma unroll
-            for (int k = 0; k < 27; ++k) acc = fmaf(__ldg(f32g + ucn::X3Layout::vd + k * 128 + row), pe[k], acc);
-            rayb_s[(s * rpt + i) * 128 + row] = acc;
-          }
-          named_bar_sync(bar_id, 256);
+          tr.ev(6, 3, g);
         } else {
           head[0] = head[1] = head[2] = head[3] = 0.f;
           epi64<2, true>(t_acc, t_mod, col0, f32s + ucn::X3Layout::b_vv, rayb_s + (s * rpt + ri) * 128, h_row,
                          f32s + ucn::X3Layout::w_adapt, head);
+          tr.ev(6, 5, g);
           if (hf == 1) {
             exch_s[s * 128 + row] = make_float4(head[0], head[1], head[2], head[3]);
             named_bar_arrive(bar_id, 256);
