@@ -184,7 +184,9 @@ def main():
             "conf": torch.from_numpy(sc.confidence).pin_memory()}
     h2d_bytes = sum(t.numel() * 4 for t in host["dv"] + host["vol"] + [host["feat"], host["imgs"], host["conf"]])
     resident = {k: ([t.to(dev) for t in v] if isinstance(v, list) else v.to(dev)) for k, v in host.items()}
-    max_rays = args.max_rays or n_rays
+    # rays per launch group: whole frame unless its staged rows would exceed ~24 GB of workspace (config 5: 124 GB)
+    per_ray = S * (4 * (24 + 12 * V + 1) + 32)
+    max_rays = args.max_rays or min(n_rays, max(W, int(24e9 // per_ray) // W * W))
 
     def pack(maps):
         fr = PackedFrame(dev)
@@ -207,7 +209,7 @@ def main():
         ren.render(seed=seed, out_rgb=rgb, out_depth=depth, timers=timers)
 
     from ucnerf_b200.frame import HostSweep
-    sweep = HostSweep(pw, pack, n_rays, args.mode, dev)
+    sweep = HostSweep(pw, pack, n_rays, args.mode, dev, max_rays=max_rays)
 
     def step_e2e(i, last):
         # view i from pinned host maps -> pinned host image; view i+1's maps cross PCIe while view i renders

@@ -313,3 +313,36 @@ def test_ray_marcher_bit_exact(name, golden_dir):
     assert np.array_equal(bits(z.cpu().numpy()), bits(z_o)) and np.array_equal(bits(z_o), bits(g[name + "_z"]))
     assert np.array_equal(bits(xyz.cpu().numpy()), bits(xyz_o)) and np.array_equal(bits(xyz_o), bits(g[name + "_xyz"]))
     assert np.array_equal(o.cpu().numpy(), rays[:, 0:3]) and np.array_equal(d.cpu().numpy(), rays[:, 3:6])
+
+
+def test_host_sweep_matches_frame_renderer():
+    """frame.HostSweep (pinned host maps -> pinned host image, next view's maps prefetched on a side stream) returns
+    exactly what FrameRenderer returns for device-resident maps, view after view."""
+    from ucnerf_b200 import synthetic
+    from ucnerf_b200.frame import FrameRenderer, HostSweep, PackedFrame, PackedWeights
+    H, W, V, S = 24, 40, 3, 126
+    pw = PackedWeights(synthetic.make_weights(V, seed=3), V, DEV)
+    scenes = [synthetic.make_scene(H, W, V, seed=30 + i) for i in range(3)]
+
+    def host_maps(sc):
+        return {"dv": [torch.from_numpy(a).pin_memory() for a in sc.depth_values],
+                "vol": [torch.from_numpy(a).pin_memory() for a in sc.volumes],
+                "feat": torch.from_numpy(sc.img_feats).pin_memory(), "imgs": torch.from_numpy(sc.imgs).pin_memory(),
+                "conf": torch.from_numpy(sc.confidence).pin_memory()}
+    maps = [host_maps(sc) for sc in scenes]
+    cur = {"sc": None}
+
+    def make_frame(dev_maps):
+        sc = cur["sc"]
+        fr = PackedFrame(DEV)
+        fr.set_target(H, W, S, sc.K[0], sc.c2ws[0], sc.w2cs[0], sc.near_fars[0, 0], sc.near_fars[0, 1],
+                      dir_rot0=sc.w2cs[0], dir_rot1=sc.w2cs[1], dir_switch=1024)
+        fr.set_sources(sc.w2cs[1:], sc.K[1:])
+        return fr.pack_depth_values(dev_maps["dv"]).pack_volumes(dev_maps["vol"]).pack_sources(
+            dev_maps["imgs"], dev_maps["feat"], dev_maps["conf"])
+    sweep = HostSweep(pw, make_frame, H * W, "bf16", DEV)
+    for i, sc in enumerate(scenes):
+        cur["sc"] = sc
+        out = sweep.render(i, maps[i], maps[i + 1] if i + 1 < len(maps) else None, seed=7).clone()
+        rgb, depth = FrameRenderer(PackedFrame.from_scene(sc, S, DEV, dir_switch=1024), pw, "bf16").render(seed=7)
+        assert torch.equal(out[:, :3], rgb.cpu()) and torch.equal(out[:, 3], depth.cpu()), i

@@ -284,9 +284,11 @@ class HostSweep:
     (train.py:274-275).  `make_frame(dev_maps)` builds the PackedFrame (cameras + ucn_pack_* of the staged maps).
     """
 
-    def __init__(self, weights: PackedWeights, make_frame, n_rays: int, mode: str = "bf16", device="cuda"):
+    def __init__(self, weights: PackedWeights, make_frame, n_rays: int, mode: str = "bf16", device="cuda",
+                 max_rays: Optional[int] = None):
         self.device = torch.device(device)
         self.weights, self.make_frame, self.mode, self.n_rays = weights, make_frame, mode, int(n_rays)
+        self.max_rays = int(max_rays or n_rays)         # rays per launch group (bounds the workspace)
         self.copy_stream = torch.cuda.Stream(device=self.device)
         self.staging = [None, None]
         self.copied = [torch.cuda.Event(), torch.cuda.Event()]
@@ -327,7 +329,7 @@ class HostSweep:
         main.wait_event(self.copied[slot])
         fr = self.make_frame(self.staging[slot])
         if self.renderer is None:
-            self.renderer = FrameRenderer(fr, self.weights, self.mode, max_rays=self.n_rays)
+            self.renderer = FrameRenderer(fr, self.weights, self.mode, max_rays=self.max_rays)
         self.renderer.frame = fr
         self.renderer.render(seed=seed, out_rgb=self.rgb, out_depth=self.depth)
         self.free[slot].record(main)
