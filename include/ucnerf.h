@@ -185,6 +185,47 @@ int ucn_mlp_forward_tiles(const ucn_weights *w, const float *ndc_pts, const floa
 int ucn_composite(const float *raw, const float *z, int R, int S, int white_bkgd, float *rgb, float *depth,
                   float *acc, float *weights, void *stream);
 
+/* ---- training step: backward kernels and the fp32 training primitives -----------
+ * The reference trains through autograd (train.py:147-190).  Sample positions carry no gradient (depth hypotheses
+ * are detached, network/mvs_models.py:716-717); gradients reach the MLP parameters, the three feature volumes, the
+ * source-view FPN features and the confidence map.  uc-nerf_b200/train_path.py wires these into torch.autograd. */
+/* K4b: backward of raw2outputs (network/renderer.py:25-36,125-131): cotangents g_rgb [R][3], g_depth [R] -> d_raw [R][S][4] */
+int ucn_composite_bwd(const float *raw, const float *z, int R, int S, int white_bkgd, const float *g_rgb,
+                      const float *g_depth, float *d_raw, void *stream);
+/* K2b: backward of the grid_sample groups of gen_pts_feats (utils/utils.py:776-788,859-890): d_feat [n][F] is
+ * scatter-added (fp32 atomics) into gradients laid out like the reference tensors: d_volK [8][D_k][h_k][w_k],
+ * d_img_feat [V][8][H][W], d_conf [H][W]; any destination may be NULL.  Only dims and cameras of `f` are read. */
+int ucn_gather_bwd(const ucn_frame *f, const float *pts, const float *ndc_s1, const float *ndc_s2, const float *ndc_s3,
+                   int64_t n_samples, const float *d_feat, float *d_vol0, float *d_vol1, float *d_vol2,
+                   float *d_img_feat, float *d_conf, void *stream);
+/* K3b primitives: nn.Linear forward / grad-input / grad-weight on row-major fp32 operands with explicit leading
+ * dimensions; W and dW in the reference's [out][in] layout (network/models.py:87-104). */
+int ucn_linear_fwd(const float *X, int64_t ldx, const float *W, int64_t ldw, const float *b, int64_t M, int K, int N,
+                   float *Y, int64_t ldy, int flags /* 1: accumulate into Y, 2: ReLU */, void *stream);
+int ucn_linear_bwd_input(const float *dY, int64_t ldy, const float *W, int64_t ldw, int64_t M, int K, int N, float *dX,
+                         int64_t ldx, int flags /* 1: accumulate into dX */, void *stream);
+/* dW += dY^T X, db += column sums of dY (atomic accumulation: zero the destinations first; db may be NULL) */
+int ucn_linear_bwd_weight(const float *dY, int64_t ldy, const float *X, int64_t ldx, int64_t M, int K, int N, float *dW,
+                          int64_t lddw, float *db, void *stream);
+/* ph[:, 0:63] = PE_10(ndc [N][3]); ftv[:, 128:155] = PE_4(angle[ray]) (network/models.py:50-54, renderer.py:88-100) */
+int ucn_train_prep(const float *ndc, const float *angle, int S, int64_t N, float *ph, int64_t ldph, float *ftv,
+                   int64_t ldftv, void *stream);
+/* h = relu(pre * mod) over [M][128] (network/models.py:154-155) and its backward (dmod optionally accumulated) */
+int ucn_film_relu_fwd(const float *pre, const float *mod, float *h, int64_t ldh, int64_t M, void *stream);
+int ucn_film_relu_bwd(const float *dh, int64_t lddh, const float *pre, const float *mod, const float *h, int64_t ldh,
+                      float *dpre, float *dmod, int accumulate, int64_t M, void *stream);
+/* o = a * b over [M][128] (h * feats_bias, network/models.py:164); backward: da (+)= do*b, db = do*a */
+int ucn_mul_fwd(const float *a, int64_t lda, const float *b, float *o, int64_t M, void *stream);
+int ucn_mul_bwd(const float *d_o, const float *a, int64_t lda, const float *b, float *da, int accumulate, float *db,
+                int64_t M, void *stream);
+int ucn_relu_bwd(const float *dy, const float *y, float *dx, int64_t n, void *stream);
+/* uncertainty-weighted blend of the base and adapt heads (network/models.py:149,177-180); conf = input_feat[..., -1] */
+int ucn_blend_fwd(const float *base4, const float *adapt4, const float *conf, int64_t ldconf, float *raw, int64_t M,
+                  void *stream);
+int ucn_blend_bwd(const float *d_raw, const float *raw, const float *base4, const float *adapt4, const float *conf,
+                  int64_t ldconf, float *d_base4, float *d_adapt4, float *d_conf, int64_t lddconf, int64_t M,
+                  void *stream);
+
 /* ---- whole frame --------------------------------------------------------------------------- */
 size_t ucn_frame_workspace_bytes(const ucn_frame *f, int R, int mode);
 /* K1 -> K2 -> K3 -> K4 for rays [ray0, ray0+R) on `stream`, everything device-resident.

@@ -217,6 +217,26 @@ def raw2outputs(raw, z):
     return rgb, depth
 
 
+def raw2outputs_bwd(raw, z, g_rgb, g_depth):
+    """Backward of raw2outputs (network/renderer.py:25-36,125-131) -> d_raw [R,S,4]."""
+    R, S = z.shape
+    d_raw = np.empty((R, S, 4), np.float32)
+    lib().uco_composite_bwd(_p(_f32(raw)), _p(_f32(z)), R, S, _p(_f32(g_rgb)), _p(_f32(g_depth)), _p(d_raw))
+    return d_raw
+
+
+def gen_pts_feats_bwd(osc: OracleScene, pts, ndc_all, d_feat):
+    """Backward of gen_pts_feats w.r.t. the sampled tensors -> (d_vol[3] [8,D,h,w], d_img_feats [V,8,H,W], d_conf [H,W])."""
+    R = pts.shape[0]
+    c = osc.c
+    dv = [np.zeros((8, c.D[k], c.h[k], c.w[k]), np.float32) for k in range(3)]
+    dfe = np.zeros((c.V, 8, c.H, c.W), np.float32)
+    dco = np.zeros((c.H, c.W), np.float32)
+    lib().uco_gather_bwd(C.byref(c), _p(_f32(pts)), _p(_f32(ndc_all)), R, _p(_f32(d_feat)), _p(dv[0]), _p(dv[1]),
+                         _p(dv[2]), _p(dfe), _p(dco))
+    return dv, dfe, dco
+
+
 def render_rays(osc: OracleScene, ow: OracleWeights, ray0: int, R: int, t_rand):
     """Whole path for rays [ray0, ray0+R) (chained C driver; used as CPU baseline)."""
     t_rand = _f32(t_rand).reshape(R, osc.S)

@@ -248,6 +248,95 @@ void uco_composite(const float *raw, const float *z, int R, int S, float *rgb, f
   }
 }
 
+/* ------------------------------------------------------------------------------------------
+ * Backward restatements (training step, train.py:147-190 through autograd).  Serial loops, double accumulators:
+ * these are the checkers of ucn_composite_bwd / ucn_gather_bwd and are pinned to the reference's autograd
+ * gradients (tests/golden/grad_*.npz).
+ * ------------------------------------------------------------------------------------------ */
+/* backward of uco_composite: cumprod backward as ATen computes it for non-zero factors (reverse cumsum of
+ * grad*out divided by the input), network/renderer.py:25-36,125-131. */
+void uco_composite_bwd(const float *raw, const float *z, int R, int S, const float *g_rgb, const float *g_depth,
+                       float *d_raw) {
+  for (int r = 0; r < R; ++r) {
+    double T = 1.0, suffix = 0.0;
+    double Ti[UCO_MAX_S], wv[UCO_MAX_S];
+    for (int i = 0; i < S; ++i) {
+      const float *s = raw + ((size_t)r * S + i) * 4;
+      const double alpha = 1.0 - exp(-(double)s[3]);
+      const double v = (double)g_rgb[3 * r] * s[0] + (double)g_rgb[3 * r + 1] * s[1] + (double)g_rgb[3 * r + 2] * s[2] +
+                       (double)g_depth[r] * z[(size_t)r * S + i];
+      Ti[i] = T;
+      wv[i] = alpha * T * v;
+      T *= (1.0 - alpha) + 1e-10;
+    }
+    for (int i = S - 1; i >= 0; --i) {
+      const float *s = raw + ((size_t)r * S + i) * 4;
+      float *d = d_raw + ((size_t)r * S + i) * 4;
+      const double e = exp(-(double)s[3]), alpha = 1.0 - e, q = (1.0 - alpha) + 1e-10, w = alpha * Ti[i];
+      const double vv = (double)g_rgb[3 * r] * s[0] + (double)g_rgb[3 * r + 1] * s[1] + (double)g_rgb[3 * r + 2] * s[2] +
+                        (double)g_depth[r] * z[(size_t)r * S + i];
+      d[0] = (float)(w * g_rgb[3 * r]); d[1] = (float)(w * g_rgb[3 * r + 1]); d[2] = (float)(w * g_rgb[3 * r + 2]);
+      d[3] = (float)(e * (Ti[i] * vv - suffix / q));
+      suffix += wv[i];
+    }
+  }
+}
+
+static inline void tri8_bwd(float *dvol, int D, int h, int w, float gx, float gy, float gz, const float *g) {
+  const float ix = clipc(unnorm(gx, w, 0), w), iy = clipc(unnorm(gy, h, 0), h), iz = clipc(unnorm(gz, D, 0), D);
+  const float fx = floorf(ix), fy = floorf(iy), fz = floorf(iz);
+  const int x0 = (int)fx, y0 = (int)fy, z0 = (int)fz;
+  const float tx = ix - fx, ty = iy - fy, tz = iz - fz;
+  const float ux = (fx + 1.0f) - ix, uy = (fy + 1.0f) - iy, uz = (fz + 1.0f) - iz;
+  const size_t cs = (size_t)D * h * w;
+  for (int corner = 0; corner < 8; ++corner) {
+    const int dx = corner & 1, dy = (corner >> 1) & 1, dz = corner >> 2;
+    const int x = x0 + dx, y = y0 + dy, zz = z0 + dz;
+    if (x >= w || y >= h || zz >= D) continue;
+    const float wgt = (dx ? tx : ux) * (dy ? ty : uy) * (dz ? tz : uz);
+    for (int c = 0; c < 8; ++c) dvol[c * cs + ((size_t)zz * h + y) * w + x] += wgt * g[c];
+  }
+}
+static inline void bil_bwd(float *dimg, int C, int H, int W, float gx, float gy, int align, const float *g) {
+  const float ix = clipc(unnorm(gx, W, align), W), iy = clipc(unnorm(gy, H, align), H);
+  const float fx = floorf(ix), fy = floorf(iy);
+  const int x0 = (int)fx, y0 = (int)fy;
+  const float tx = ix - fx, ty = iy - fy, ux = (fx + 1.0f) - ix, uy = (fy + 1.0f) - iy;
+  for (int corner = 0; corner < 4; ++corner) {
+    const int dx = corner & 1, dy = corner >> 1;
+    const int x = x0 + dx, y = y0 + dy;
+    if (x >= W || y >= H) continue;
+    const float wgt = (dx ? tx : ux) * (dy ? ty : uy);
+    for (int c = 0; c < C; ++c) dimg[(size_t)c * H * W + (size_t)y * W + x] += wgt * g[c];
+  }
+}
+/* backward of uco_gather (grid_sample backward w.r.t. the sampled tensors, utils/utils.py:776-788,859-890):
+ * d_feat [R][S][F] -> d_vol[k] [8,D_k,h_k,w_k], d_feats [V,8,H,W], d_conf [H,W] (accumulated; caller zeroes). */
+void uco_gather_bwd(const uco_scene *sc, const float *pts, const float *ndc, int R, const float *d_feat,
+                    float *d_vol0, float *d_vol1, float *d_vol2, float *d_feats, float *d_conf) {
+  const int S = sc->S, V = sc->V, F = 24 + 12 * V + 1;
+  const float iw = (float)(sc->W - 1), ih = (float)(sc->H - 1);
+  const size_t plane = (size_t)R * S * 3, HW = (size_t)sc->H * sc->W;
+  float *dv[3] = {d_vol0, d_vol1, d_vol2};
+  for (long q = 0; q < (long)R * S; ++q) {
+    const float *g = d_feat + (size_t)q * F;
+    for (int k = 0; k < 3; ++k) {
+      const float *c = ndc + k * plane + 3 * q;
+      tri8_bwd(dv[k], sc->D[k], sc->h[k], sc->w[k], c[0] * 2 - 1.0f, c[1] * 2 - 1.0f, c[2] * 2 - 1.0f, g + 8 * k);
+    }
+    {
+      const float *c = ndc + 2 * plane + 3 * q;
+      bil_bwd(d_conf, 1, sc->H, sc->W, c[0] * 2 - 1.0f, c[1] * 2 - 1.0f, 0, g + F - 1);
+    }
+    const float *p = pts + 3 * q;
+    for (int v = 0; v < V; ++v) {
+      float nx, ny, pz;
+      project(sc->src_w2c + 16 * v, sc->src_K + 9 * v, iw, ih, p, &nx, &ny, &pz);
+      bil_bwd(d_feats + (size_t)v * 8 * HW, 8, sc->H, sc->W, nx * 2.0f - 1.0f, ny * 2.0f - 1.0f, 1, g + 24 + 4 * V + 8 * v);
+    }
+  }
+}
+
 /* data/ray_utils.py:152-197 ray_marcher.  rays [R][8] = (o, d, near, far); t = linspace(0,1,S); rnd [R][S] uniforms
  * (used when perturb > 0).  xyz [R][S][3], z [R][S].  Every elementwise op of the reference rounds on its own. */
 static inline float marcher_z(float near, float far, float t, int lindisp) {

@@ -53,6 +53,11 @@ void uco_render_rays(const uco_scene *sc, const uco_weights *wt, int ray0, int R
                      const float *t_rand, float *rgb, float *depth);
 void uco_ray_marcher(const float *rays, int R, int S, const float *t, const float *rnd, float perturb, int lindisp,
                      float *xyz, float *z);
+/* backward restatements (training step): checkers of ucn_composite_bwd / ucn_gather_bwd */
+void uco_composite_bwd(const float *raw, const float *z, int R, int S, const float *g_rgb, const float *g_depth,
+                       float *d_raw);
+void uco_gather_bwd(const uco_scene *sc, const float *pts, const float *ndc, int R, const float *d_feat,
+                    float *d_vol0, float *d_vol1, float *d_vol2, float *d_feats, float *d_conf);
 int uco_num_threads(void);
 void uco_set_num_threads(int n);
 #endif

@@ -22,3 +22,23 @@ def load_case(name):
 
 def bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+GRAD_CASES = ("grad_small_v3", "grad_small_v5")
+
+
+def load_grad_case(name):
+    """Golden gradients of the reference's autograd (tests/golden/make_golden_grad.py) + the forward case they extend."""
+    g = dict(np.load(os.path.join(GOLDEN_DIR, f"{name}.npz")))
+    c = load_case(str(g["base"]))
+    R = int(g["meta"][4])
+    rng = np.random.default_rng(9000 + c["seed"])
+    g_rgb = rng.standard_normal((R, 3)).astype(np.float32)
+    g_depth = rng.standard_normal((R,)).astype(np.float32)
+    c.update(gg=g, R=R, g_rgb=g_rgb, g_depth=g_depth)
+    return c
+
+
+def rel_err(a, b):
+    """max |a-b| relative to the largest magnitude of the expected tensor (gradients span decades)."""
+    return float(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64)).max() / max(np.abs(b).max(), 1e-30))

@@ -69,6 +69,22 @@ _SIGS = {
     "ucn_dir_feature": (C.c_int, [C.POINTER(Frame), _fp, C.c_int, C.c_int, _fp, _fp]),
     "ucn_mlp_forward": (C.c_int, [C.POINTER(Weights), _fp, _fp, _fp, C.c_int, C.c_int, _fp, C.c_int, _fp]),
     "ucn_composite": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, _fp]),
+    "ucn_composite_bwd": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp]),
+    "ucn_gather_bwd": (C.c_int, [C.POINTER(Frame), _fp, _fp, _fp, _fp, C.c_int64, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "ucn_linear_fwd": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, _fp, C.c_int64, C.c_int, C.c_int, _fp, C.c_int64,
+                                 C.c_int, _fp]),
+    "ucn_linear_bwd_input": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, C.c_int64, C.c_int, C.c_int, _fp, C.c_int64,
+                                       C.c_int, _fp]),
+    "ucn_linear_bwd_weight": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, C.c_int64, C.c_int, C.c_int, _fp, C.c_int64,
+                                        _fp, _fp]),
+    "ucn_train_prep": (C.c_int, [_fp, _fp, C.c_int, C.c_int64, _fp, C.c_int64, _fp, C.c_int64, _fp]),
+    "ucn_film_relu_fwd": (C.c_int, [_fp, _fp, _fp, C.c_int64, C.c_int64, _fp]),
+    "ucn_film_relu_bwd": (C.c_int, [_fp, C.c_int64, _fp, _fp, _fp, C.c_int64, _fp, _fp, C.c_int, C.c_int64, _fp]),
+    "ucn_mul_fwd": (C.c_int, [_fp, C.c_int64, _fp, _fp, C.c_int64, _fp]),
+    "ucn_mul_bwd": (C.c_int, [_fp, _fp, C.c_int64, _fp, _fp, C.c_int, _fp, C.c_int64, _fp]),
+    "ucn_relu_bwd": (C.c_int, [_fp, _fp, _fp, C.c_int64, _fp]),
+    "ucn_blend_fwd": (C.c_int, [_fp, _fp, _fp, C.c_int64, _fp, C.c_int64, _fp]),
+    "ucn_blend_bwd": (C.c_int, [_fp, _fp, _fp, _fp, _fp, C.c_int64, _fp, _fp, _fp, C.c_int64, C.c_int64, _fp]),
     "ucn_frame_workspace_bytes": (C.c_size_t, [C.POINTER(Frame), C.c_int, C.c_int]),
     "ucn_render_rays": (C.c_int, [C.POINTER(Frame), C.POINTER(Weights), C.c_int, C.c_int, _fp, _fp, C.c_uint64,
                                   C.c_int, _fp, C.c_size_t, _fp, _fp, _fp]),
