@@ -26,7 +26,7 @@ def _host(x, shape=None) -> np.ndarray:
 def _dev(x, device) -> torch.Tensor:
     if isinstance(x, np.ndarray):
         x = torch.from_numpy(np.ascontiguousarray(x))
-    return x.to(device=device, dtype=torch.float32).contiguous()
+    return x.detach().to(device=device, dtype=torch.float32).contiguous()
 
 
 def linspace01(n: int, device) -> torch.Tensor:

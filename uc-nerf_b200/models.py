@@ -6,7 +6,9 @@
 ``UCNeRF`` keeps the reference's parameter names and shapes (``state_dict()`` keys ``nerf.*``, including the
 three layers forward() never uses, Q9) so released ``.tar`` checkpoints load unchanged; ``forward`` runs
 the fused CUDA kernel (PE + 13 linear layers + FiLM + uncertainty blend) -- fp32 SIMT (`mode='fp32'`) or
-bf16 tcgen05 (`mode='bf16'`).  Forward only: training/backward kernels are a later row of SURVEY.md §8.
+bf16 tcgen05 (`mode='bf16'`).  When autograd is recording and a parameter or the feature rows require grad (the
+training step, train.py:147-190), ``forward_fused`` switches to the fp32 training primitives and their backward
+(train_path.MlpFn).
 """
 from __future__ import annotations
 
@@ -17,6 +19,7 @@ import torch
 import torch.nn as nn
 
 from . import lib as L
+from . import train_path as _tp
 from .frame import PackedWeights
 
 
@@ -138,6 +141,10 @@ class UCNeRF(nn.Module):
     def forward_fused(self, ndc_pts, viewdirs, feats, mode: Optional[str] = None):
         """ndc_pts [R,S,3], viewdirs [R,3] (per ray), feats [R,S,F] -> raw [R,S,4] = (rgb, sigma)."""
         R, S = feats.shape[:2]
+        if _tp.wants_grad(feats, *self.parameters()):
+            # training step (train.py:147-190): fp32 primitives with saved activations + their backward (K3b)
+            named = dict(self.nerf.named_parameters())
+            return _tp.MlpFn.apply(ndc_pts, viewdirs, feats, S, *[named[n] for n in _tp.PARAM_NAMES])
         pw = self.packed()
         raw = torch.empty((R, S, 4), device=feats.device)
         args = [t.to(torch.float32).contiguous() for t in (ndc_pts, feats, viewdirs)]

@@ -18,6 +18,7 @@ from typing import Dict, Optional
 import torch
 
 from . import lib as L
+from . import train_path as _tp
 from .frame import PackedFrame, linspace01
 
 _FRAME_CACHE: Dict[tuple, PackedFrame] = {}
@@ -220,6 +221,12 @@ def gather_features(volume_feature, imgs, img_feat, confidence, pose_ref, rays_p
     if rays_ndc is None:
         rays_ndc = {k: rays_pts for k in ("stage1", "stage2", "stage3")}
     R, S = rays_pts.shape[:2]
+    if parts == L.PART_ALL and not with_idx and volume_feature is not None and imgs is not None:
+        vols = [volume_feature[s]["volume_feature_no_ref"] for s in ("stage1", "stage2", "stage3")]
+        if _tp.wants_grad(*vols, img_feat, confidence):
+            # training step: K2 with its backward K2b (gradients for the volumes, FPN features, confidence)
+            return _tp.GatherFn.apply(fr, rays_pts, rays_ndc["stage1"], rays_ndc["stage2"], rays_ndc["stage3"], *vols,
+                                      img_feat, confidence)
     feat = torch.empty((R, S, fr.F), device=rays_pts.device)
     idx = torch.empty((R, S, 11 + 3 * fr.c.V), device=rays_pts.device, dtype=torch.int32) if with_idx else None
     args = [rays_pts, rays_ndc["stage1"], rays_ndc["stage2"], rays_ndc["stage3"]]

@@ -17,6 +17,7 @@ import torch
 
 from . import lib as L
 from . import rays as _rays
+from . import train_path as _tp
 from .frame import PackedFrame
 
 
@@ -31,6 +32,9 @@ def _composite(raw, z_vals, white_bkgd, want_weights):
     if not raw.is_cuda:
         raise L.UcnError("raw2outputs: tensors must be on a CUDA device (no CPU fallback exists)")
     R, S = z_vals.shape
+    if not want_weights and _tp.wants_grad(raw):      # training step: K4 with its backward K4b (train.py:147-190)
+        rgb, depth = _tp.CompositeFn.apply(raw, z_vals, white_bkgd)
+        return rgb, depth, None, None
     raw4 = raw[..., :4].to(torch.float32).contiguous()
     z = z_vals.to(torch.float32).contiguous()
     rgb = torch.empty((R, 3), device=raw.device)
