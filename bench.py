@@ -2,7 +2,7 @@
 """bench.py -- rays/s of the UC-NeRF per-ray rendering hot path on B200 (BASELINE.json metric).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode bf16|fp32]
-                    [--workload c2|c1|c5] [--max-rays M]
+                    [--workload c2|c1|c5|c4] [--max-rays M]
 
 A "step" renders one whole target view of the workload: K0 pack of that view's maps + K1 raygen/sampling
 + K2 projection/gathers + K3 PE+MLP + K4 compositing.  `value` = rays of all ranks / max-over-ranks device
@@ -31,6 +31,8 @@ WORKLOADS = {
                                               "(reference rejects 128: N_samples%3), random-init weights"),
     "c1": dict(H=256, W=320, V=3, S=126, name="UC-NeRF eval render 320x256, 3 source views, 126 samples/ray"),
     "c5": dict(H=1024, W=1280, V=5, S=255, name="High-res stress 1280x1024, 5 source views, 255 samples/ray"),
+    # BASELINE.json configs[3]: training step + NCCL gradient all-reduce (bench_train.py)
+    "c4": dict(H=256, W=320, V=3, S=126, name="UC-NeRF training step, 2048 rays, NCCL grad all-reduce"),
 }
 FLOP_PER_SAMPLE = lambda V: 2 * (138112 + 1536 * V)          # SURVEY.md §8.0 (algorithmic MLP FLOPs)
 FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
@@ -156,6 +158,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
+    if args.workload == "c4":
+        import bench_train
+        return bench_train.run_reference(args) if args.impl == "reference" else bench_train.run(args, ClockSampler, peaks)
     if args.impl == "reference":
         return run_reference(args, wl)
 

@@ -5,6 +5,7 @@ Same names, argument order, return tuples and tensor shapes as the reference fun
     utils/utils.py:217   get_rays_mvs            utils/utils.py:600   build_rays_test
     utils/utils.py:323   get_ndc_coordinate      utils/utils.py:393   sample_points_uniform
     utils/utils.py:742   build_color_volume      utils/utils.py:833   index_point_feature
+    utils/utils.py:400   build_rays (training sampler; selection in PyTorch, sampling on K1)
     data/ray_utils.py:12 get_ray_directions      data/ray_utils.py:32 get_rays
     data/ray_utils.py:152 ray_marcher
 
@@ -249,3 +250,79 @@ def build_color_volume(point_samples, pose_ref, imgs, near_far=None, img_feat=No
     V = imgs.shape[1]
     feat = gather_features(None, imgs, img_feat, None, pose_ref, point_samples, None, parts=L.PART_VIEWS)
     return feat[..., 24:24 + (12 if img_feat is not None else 4) * V]
+
+
+# ---- training sampler -------------------------------------------------------------------
+
+def select_training_pixels(H, W, confidence, coords, N_rays, patch_num, patch_size, generator=None):
+    """Ray SELECTION of build_rays (utils/utils.py:450-479,169-215,217-247,274-320), kept in PyTorch as the survey
+    prescribes: patch_num/2 patches drawn by confidence-multinomial, patch_num/2 by (1 - confidence), uniform random
+    pixels up to N_rays, then the sparse-depth coordinates.  The reference's per-patch Python loop is replaced by one
+    vectorised index computation (same distribution).  -> pixel_coordinates [2, R] (row, col), float32."""
+    device = confidence.device
+    ps, half = int(patch_size), int(patch_num) // 2
+    if N_rays < 2 * half * ps * ps:
+        raise L.UcnError("batch_size must be >= patch_num * patch_size^2 (utils/utils.py:468-474, quirk Q20)")
+    conf = confidence.detach().reshape(-1).float()
+    grid = torch.arange(ps, device=device)
+    pix = []
+    for weights in (conf, 1.0 - conf):
+        sel = torch.multinomial(weights, half, generator=generator)
+        pi = torch.clamp(torch.div(sel, W, rounding_mode="floor") // ps, 0, H // ps - 2)
+        pj = torch.clamp((sel % W) // ps, 0, W // ps - 2)
+        si = torch.randint(0, ps, (half,), device=device, generator=generator)
+        sj = torch.randint(0, ps, (half,), device=device, generator=generator)
+        rows = (pi * ps + si)[:, None, None] + grid[None, :, None]            # [half, ps, 1]
+        cols = (pj * ps + sj)[:, None, None] + grid[None, None, :]            # [half, 1, ps]
+        pix.append(torch.stack((rows.expand(-1, ps, ps).reshape(-1), cols.expand(-1, ps, ps).reshape(-1))))
+    n_rand = N_rays - 2 * half * ps * ps
+    xs = torch.randint(0, W, (n_rand,), device=device, generator=generator)
+    ys = torch.randint(0, H, (n_rand,), device=device, generator=generator)
+    pix.append(torch.stack((ys, xs)))
+    if coords is not None:
+        pix.append(coords.to(device).t().long())                              # coords [N,2] = (row, col)
+    return torch.cat(pix, dim=1).float()
+
+
+def build_rays(args, imgs, mvs_confidence, sparse_depths, coords, pose_ref, w2cs, c2ws, intrinsics, N_rays, N_samples,
+               pad=0, is_precrop_iters=False, ref_idx=0, with_depth=False, outputs=None,
+               pixel_coordinates: Optional[torch.Tensor] = None, t_rand: Optional[torch.Tensor] = None, seed: int = 0):
+    """utils/utils.py:400-597 (training sampler).  Returns the reference's 9-tuple
+    (ray_coordinate_world [R,S,3], ray_dir_world [R,3], colors [R,3], points_all {stage1,stage2,stage3,ndc},
+    depth_candidates [R,S], rays_os [R,3], rays_depths (None), ndc_parameters, pixel_coordinates_int [2,R]).
+
+    Selection stays in PyTorch (`select_training_pixels`); everything after it -- ray directions, per-pixel stage
+    near/far, 3 x S/3 sweeps, sort, jitter, world points, the four NDC tensors -- is K1's explicit-pixel mode, the
+    same arithmetic as `build_rays_test`.  Extensions: `pixel_coordinates` injects a selection (parity tests),
+    `t_rand` injects the jitter the reference draws with torch.rand (:572)."""
+    if not with_depth:
+        raise L.UcnError("build_rays(with_depth=False) is dead in the reference (depth_candidate undefined, "
+                         "utils/utils.py:575); train.py:147 always passes with_depth=True")
+    _need_cuda(imgs, "build_rays")
+    device = imgs.device
+    N, V, C3, H, W = imgs.shape
+    S = int(N_samples)
+    if pixel_coordinates is None:
+        pixel_coordinates = select_training_pixels(H, W, mvs_confidence, coords, N_rays, args.patch_num, args.patch_size)
+    pix = pixel_coordinates.to(device=device, dtype=torch.float32).contiguous()
+    R = pix.shape[1]
+    w2c_ref, intrinsic_ref = pose_ref['w2cs'][ref_idx], pose_ref['intrinsics'][ref_idx]
+    near, far = pose_ref['near_fars'][ref_idx, 0], pose_ref['near_fars'][ref_idx, 1]
+    fr = _rays_frame(int(H), int(W), S, c2ws[0], w2c_ref, intrinsics[0], float(near), float(far), outputs)
+    z = torch.empty((R, S), device=device)
+    rays_d = torch.empty((R, 3), device=device)
+    pts = torch.empty((R, S, 3), device=device)
+    ndc = torch.empty((4, R, S, 3), device=device)
+    if t_rand is not None:
+        t_rand = t_rand.to(device=device, dtype=torch.float32).contiguous()
+        assert tuple(t_rand.shape) == (R, S)
+    L.check(L.load().ucn_raygen_sample(C.byref(fr.c), L.ptr(pix), 0, R, L.ptr(fr.t_vals), L.ptr(t_rand), int(seed),
+                                       L.ptr(z), L.ptr(rays_d), L.ptr(pts), L.ptr(ndc), L.stream_ptr()),
+            "ucn_raygen_sample")
+    pix_int = pix.long()
+    colors = imgs[0, 0][:, pix_int[0], pix_int[1]].permute(1, 0)              # :497-501, target view = index 0
+    rays_o = c2ws[0][:3, -1].clone().reshape(1, 3).expand(R, -1)
+    ndc_parameters = {"w2c_ref": w2c_ref, "intrinsic_ref": intrinsic_ref,
+                      "inv_scale": torch.tensor([W - 1, H - 1]).to(device), "near": near, "far": far, "pad": pad}
+    points_all = {"stage1": ndc[0], "stage2": ndc[1], "stage3": ndc[2], "ndc": ndc[3]}
+    return pts, rays_d, colors, points_all, z, rays_o, None, ndc_parameters, pix_int

@@ -269,3 +269,34 @@ class GatherFn(torch.autograd.Function):
 
 def wants_grad(*tensors) -> bool:
     return torch.is_grad_enabled() and any(t is not None and getattr(t, "requires_grad", False) for t in tensors)
+
+
+# ---- data-parallel gradient exchange (SURVEY.md 8e "Collective (train)") --------------------------------------------
+
+def allreduce_grads(params, world_size: int, bucket: "torch.Tensor | None" = None):
+    """One all-reduce(sum)/P per step over a flat fp32 bucket of every parameter gradient (NCCL over NVLink on the
+    GPU box, gloo in the CPU tests); parameters without a gradient (the three unused layers, Q9) contribute zeros so
+    that every rank reduces the same bucket.  Returns the bucket (reusable across steps)."""
+    import torch.distributed as dist
+    params = list(params)
+    n = sum(p.numel() for p in params)
+    if bucket is None or bucket.numel() != n:
+        bucket = torch.empty((n,), device=params[0].device, dtype=torch.float32)
+    o = 0
+    for p in params:
+        k = p.numel()
+        if p.grad is None:
+            bucket[o:o + k].zero_()
+        else:
+            bucket[o:o + k].copy_(p.grad.reshape(-1))
+        o += k
+    if world_size > 1:
+        dist.all_reduce(bucket, op=dist.ReduceOp.SUM)
+        bucket.div_(world_size)
+    o = 0
+    for p in params:
+        k = p.numel()
+        if p.grad is not None:
+            p.grad.copy_(bucket[o:o + k].view_as(p.grad))
+        o += k
+    return bucket
