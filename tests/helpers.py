@@ -42,3 +42,18 @@ def load_grad_case(name):
 def rel_err(a, b):
     """max |a-b| relative to the largest magnitude of the expected tensor (gradients span decades)."""
     return float(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64)).max() / max(np.abs(b).max(), 1e-30))
+
+
+TRAIN_RAY_CASES = ("train_rays_small_v3", "train_rays_s126_v3")
+
+
+def load_train_rays_case(name):
+    """Golden output of the reference's training sampler build_rays (tests/golden/make_golden_train_rays.py)."""
+    g = dict(np.load(os.path.join(GOLDEN_DIR, f"{name}.npz")))
+    c = load_case(str(g["base"]))
+    H, W, V, S, N_rays, patch_num, patch_size, n_depth, seed = (int(x) for x in g["meta"])
+    rng = np.random.default_rng(8000 + seed)
+    target = rng.random((3, H, W), dtype=np.float32)
+    coords = np.stack((rng.integers(0, H, n_depth), rng.integers(0, W, n_depth)), 1).astype(np.int64)
+    c.update(tg=g, N_rays=N_rays, patch_num=patch_num, patch_size=patch_size, n_depth=n_depth, target=target, coords=coords)
+    return c

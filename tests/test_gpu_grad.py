@@ -181,3 +181,45 @@ def test_drop_in_training_step_gradients(name):
     with torch.no_grad():
         after = model.forward_fused(ndc["ndc"], unit, zeros)
     assert float((after - before).abs().max()) > 0
+
+
+@pytest.mark.parametrize("name", ("train_rays_small_v3", "train_rays_s126_v3"))
+def test_build_rays_matches_reference_sampler(name):
+    """a13: drop-in build_rays (selection injected) vs the reference's build_rays output, bit-exact."""
+    from helpers import bits, load_train_rays_case
+    from test_gpu_parity import ref_inputs
+    from ucnerf_b200 import rays
+    c = load_train_rays_case(name)
+    g = c["tg"]
+    outputs, pose_ref, src_imgs, conf = ref_inputs(c)
+    H, W, S, V = c["H"], c["W"], c["S"], c["V"]
+    imgs = torch.cat([T(c["target"])[None, None], src_imgs.reshape(1, V, 3, H, W)], dim=1)
+    args = SimpleNamespace(patch_num=c["patch_num"], patch_size=c["patch_size"])
+    pts, dirs, colors, ndc, z, rays_o, rays_depths, ndcp, pix = rays.build_rays(
+        args, imgs, conf, None, T(c["coords"]), pose_ref, pose_ref["w2cs"], pose_ref["c2ws"], pose_ref["intrinsics"],
+        c["N_rays"], S, with_depth=True, outputs=outputs, pixel_coordinates=T(g["pix"]), t_rand=T(g["t_rand"]))
+    for got, key in ((z, "z"), (dirs, "rays_d"), (pts, "pts"), (colors, "colors"), (rays_o, "rays_o")):
+        assert np.array_equal(bits(got.cpu().numpy()), bits(g[key])), key
+    for k in ("stage1", "stage2", "stage3", "ndc"):
+        assert np.array_equal(bits(ndc[k].cpu().numpy()), bits(g[k])), k
+    assert np.array_equal(pix.cpu().numpy(), g["pix"]) and rays_depths is None
+    with pytest.raises(Exception):
+        rays.build_rays(args, imgs, conf, None, T(c["coords"]), pose_ref, pose_ref["w2cs"], pose_ref["c2ws"],
+                        pose_ref["intrinsics"], c["N_rays"], S, with_depth=False, outputs=outputs)
+
+
+def test_training_pixel_selection_properties():
+    """Selection stays in PyTorch: counts, bounds, patch structure, sparse-depth rays last (utils/utils.py:450-496)."""
+    from ucnerf_b200 import rays
+    H, W, ps, pn, N = 64, 80, 4, 10, 256
+    conf = torch.rand((1, H, W), device=DEV)
+    coords = torch.stack((torch.randint(0, H, (50,)), torch.randint(0, W, (50,))), 1).to(DEV)
+    pix = rays.select_training_pixels(H, W, conf, coords, N, pn, ps)
+    assert tuple(pix.shape) == (2, N + 50) and pix.dtype == torch.float32
+    assert float(pix[0].min()) >= 0 and float(pix[0].max()) <= H - 1 and float(pix[1].min()) >= 0 and float(pix[1].max()) <= W - 1
+    patches = pix[:, :pn * ps * ps].reshape(2, pn, ps, ps)
+    assert torch.equal(patches[0, :, 1:, :] - patches[0, :, :-1, :], torch.ones_like(patches[0, :, 1:, :]))   # rows step by 1
+    assert torch.equal(patches[1, :, :, 1:] - patches[1, :, :, :-1], torch.ones_like(patches[1, :, :, 1:]))   # cols step by 1
+    assert torch.equal(pix[:, N:].long(), coords.t())
+    with pytest.raises(Exception):
+        rays.select_training_pixels(H, W, conf, coords, pn * ps * ps - 1, pn, ps)        # quirk Q20

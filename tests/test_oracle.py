@@ -78,3 +78,22 @@ def test_ray_marcher_bit_exact(name, golden_dir):
     xyz, z = O.ray_marcher(rays, c["S"], c["lindisp"], c["perturb"], rnd)
     assert np.array_equal(bits(z), bits(g[name + "_z"]))
     assert np.array_equal(bits(xyz), bits(g[name + "_xyz"]))
+
+
+@pytest.mark.parametrize("name", ("train_rays_small_v3", "train_rays_s126_v3"))
+def test_training_sampler_positions_bit_exact(name):
+    """a13: the reference's build_rays (utils/utils.py:400-597) on its own pixel selection and jitter."""
+    from helpers import load_train_rays_case
+    c = load_train_rays_case(name)
+    g = c["tg"]
+    osc = O.OracleScene(c["scene"], c["S"], dir_switch=1 << 30)
+    pix = g["pix"].astype(np.float32)
+    r = O.build_rays_test(osc, pix[0], pix[1], g["t_rand"])
+    assert np.array_equal(bits(r["z"]), bits(g["z"]))
+    assert np.array_equal(bits(r["rays_d"]), bits(g["rays_d"]))
+    assert np.array_equal(bits(r["pts"]), bits(g["pts"]))
+    for k in ("stage1", "stage2", "stage3", "ndc"):
+        assert np.array_equal(bits(r["ndc"][k]), bits(g[k])), k
+    # the sparse-depth rays come last, in the order of the coordinate list (utils/utils.py:490-496)
+    assert np.array_equal(g["pix"][:, c["N_rays"]:], c["coords"].T)
+    assert np.array_equal(g["colors"], c["target"][:, g["pix"][0], g["pix"][1]].T)
