@@ -6,7 +6,7 @@ Driven by `bench.py --workload c4` (same flags, same JSON contract).  A "step" i
 confidence require grad), batch_size 1024 (50 confidence-drawn 4x4 patches + 224 random rays) + 1024 sparse-depth
 rays = 2 048 rays:
 
-    build_rays (selection in PyTorch, sampling on K1)  ->  rendering (K2, K3 fp32 training primitives, K4)
+    build_rays (selection in PyTorch, sampling on K1)  ->  rendering (K2, K3 training primitives, K4)
     ->  loss = 5 * img2mse + 0.05 * weighted sparse-depth MSE      (train.py:171-188; the patch smoothness /
         scale-invariant terms and cas_mvsnet_loss act on encoder outputs and are 8(f) "next" rows)
     ->  backward (K4b, K3b, K2b)  ->  one all-reduce(sum)/P of the flat gradient bucket  ->  Adam step
@@ -217,19 +217,20 @@ def run(args, ClockSampler, peaks):
         line = {
             "metric": "rays/sec", "value": world * R / (ms * 1e-3), "unit": "rays/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": NAME, **CFG, "rays_per_step_per_gpu": R, "optimizer": "Adam",
+                       "arithmetic": "fp32 operands split into three bf16 parts, six tcgen05 MMAs per product, fp32 accumulate (fp32-class: gradients within 1e-4 of the reference's autograd); heads and elementwise in fp32",
                        "loss": "5*img2mse + 0.05*weighted sparse-depth MSE (train.py:183-188)",
                        "l2": "saved activations 2.7 GB per step exceed the 126 MB L2",
                        "parallelism": f"data parallel x{world}: one all-reduce of {n_grad_params} fp32 gradients per step"},
             "e2e": {"value": world * R / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": n_depth * 16,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
             "gpu_launches": launches, "clocks": clocks,
-            "roofline": {"kernel": "gemm_kernel (fp32 SIMT nn.Linear forward / grad-input / grad-weight)", "bound": "tensor",
+            "roofline": {"kernel": "gemm_tc_kernel (nn.Linear forward / grad-input / grad-weight on tcgen05, three bf16 parts per fp32 operand)", "bound": "tensor",
                          "achieved": achieved, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
                          "frac": achieved / pk["bf16_tflops_sustained"], "traffic": None,
                          "peak_source": pk["_source"] + " (bf16_tflops_sustained)",
-                         "note": "first-cut fp32 CUDA-core GEMM; time = forward + backward phases of the step",
+                         "note": "algorithmic FLOPs (3 x forward) over the forward + backward phases of the step, which also hold the gathers, elementwise and head kernels; six MMAs are issued per algorithmic product",
                          "flops_per_step": flops, "ms": fb_ms},
             "kernels_ms_per_step": kern, "wall_ms_per_step": wall_ms,
             "loss_first_last": [loss0, box["loss"]],

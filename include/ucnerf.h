@@ -200,6 +200,9 @@ int ucn_gather_bwd(const ucn_frame *f, const float *pts, const float *ndc_s1, co
                    float *d_img_feat, float *d_conf, void *stream);
 /* K3b primitives: nn.Linear forward / grad-input / grad-weight on row-major fp32 operands with explicit leading
  * dimensions; W and dW in the reference's [out][in] layout (network/models.py:87-104). */
+/* 0 (default): products that fill a 128-wide tile run on tcgen05 with split-bf16 operands (a_hi*b_hi + a_lo*b_hi +
+ * a_hi*b_lo, fp32 accumulate in TMEM); 1: fp32 CUDA cores only. */
+int ucn_train_gemm_mode(int mode);
 int ucn_linear_fwd(const float *X, int64_t ldx, const float *W, int64_t ldw, const float *b, int64_t M, int K, int N,
                    float *Y, int64_t ldy, int flags /* 1: accumulate into Y, 2: ReLU */, void *stream);
 int ucn_linear_bwd_input(const float *dY, int64_t ldy, const float *W, int64_t ldw, int64_t M, int K, int N, float *dX,

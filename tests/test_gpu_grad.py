@@ -2,7 +2,9 @@
 against gradients produced by the reference's own autograd (tests/golden/grad_*.npz) and the CPU oracle.
 
 Gate: gradients are fp32 sums of up to 10^5 terms accumulated with atomics, so the bound is relative to the largest
-entry of each gradient tensor: 1e-4 (the reference's own CPU-vs-GPU autograd differs at the 1e-5 level)."""
+entry of each gradient tensor: 1e-4, for the nn.Linear products on the fp32 CUDA cores and on tcgen05 alike (three
+bf16 parts per operand = 24 significant bits; a two-part split was measured at 2.6e-3: its forward error flips ReLU
+masks, and a flipped mask moves a gradient sum by a whole term)."""
 import ctypes as C
 from types import SimpleNamespace
 
@@ -18,6 +20,16 @@ pytestmark = pytest.mark.gpu
 
 DEV = "cuda"
 TOL = 1e-4
+GEMM_MODES = ((1, 1e-4), (0, 1e-4))        # (ucn_train_gemm_mode, gradient gate)
+
+
+@pytest.fixture(params=GEMM_MODES, ids=("simt_fp32", "tcgen05_bf16x3parts"))
+def gemm(request):
+    from ucnerf_b200 import lib as L
+    mode, tol = request.param
+    L.check(L.load().ucn_train_gemm_mode(mode))
+    yield tol
+    L.check(L.load().ucn_train_gemm_mode(0))
 
 
 def T(a):
@@ -32,35 +44,44 @@ def _oracle_inputs(c):
     return osc, r, O.gen_pts_feats(osc, r["pts"], r["ndc_all"]), O.dir_feature(osc, r["rays_d"])
 
 
-def test_linear_primitives_match_torch():
-    """ucn_linear_fwd / _bwd_input / _bwd_weight on strided views and ragged sizes vs torch fp32 matmul."""
+@pytest.mark.parametrize("gemm_mode,tol", ((1, 1e-5), (0, 1e-5)))
+def test_linear_primitives_match_torch(gemm_mode, tol):
+    """ucn_linear_fwd / _bwd_input / _bwd_weight on strided views and ragged sizes vs torch fp64 matmul, on the fp32
+    CUDA-core kernel (mode 1) and on the tcgen05 kernel (mode 0: three bf16 parts per operand, six MMAs per K step)."""
+    from ucnerf_b200 import lib as L
     from ucnerf_b200.train_path import CudaOps
     ops = CudaOps()
-    g = torch.Generator(device="cpu").manual_seed(0)
-    for M, K, N in ((1000, 191, 128), (257, 63, 128), (4099, 128, 3), (130, 37, 128), (64, 155, 64), (5, 128, 1)):
-        Xb = torch.randn((M, K + 5), generator=g).to(DEV)
-        W = torch.randn((N, K + 3), generator=g).to(DEV)
-        b = torch.randn((N,), generator=g).to(DEV)
-        X, Wv = Xb[:, 2:2 + K], W[:, 1:1 + K]
-        Yb = torch.zeros((M, N + 2), device=DEV)
-        Y = Yb[:, 1:1 + N]
-        ops.linear_fwd(X, Wv, b, Y)
-        ref = X.double() @ Wv.double().t() + b.double()
-        assert rel_err(Y.cpu().numpy(), ref.cpu().numpy()) <= 1e-5, (M, K, N)
-        ops.linear_fwd(X, Wv, None, Y, accumulate=True, relu=True)
-        ref2 = torch.relu(ref + X.double() @ Wv.double().t())
-        assert rel_err(Y.cpu().numpy(), ref2.cpu().numpy()) <= 1e-5, (M, K, N)
-        dY = torch.randn((M, N), generator=g).to(DEV)
-        dX = torch.full((M, K), 7.0, device=DEV)
-        ops.linear_bwd_input(dY, Wv, dX)
-        assert rel_err(dX.cpu().numpy(), (dY.double() @ Wv.double()).cpu().numpy()) <= 1e-5
-        ops.linear_bwd_input(dY, Wv, dX, accumulate=True)
-        assert rel_err(dX.cpu().numpy(), (2 * dY.double() @ Wv.double()).cpu().numpy()) <= 1e-5
-        dWb, db = torch.zeros((N, K + 3), device=DEV), torch.zeros((N,), device=DEV)
-        ops.linear_bwd_weight(dY, X, dWb[:, 1:1 + K], db)
-        assert rel_err(dWb[:, 1:1 + K].cpu().numpy(), (dY.double().t() @ X.double()).cpu().numpy()) <= 1e-5
-        assert rel_err(db.cpu().numpy(), dY.double().sum(0).cpu().numpy()) <= 1e-5
-        assert float(dWb[:, 0].abs().max()) == 0.0 and float(dWb[:, 1 + K:].abs().max()) == 0.0
+    L.check(L.load().ucn_train_gemm_mode(gemm_mode))
+    try:
+        g = torch.Generator(device="cpu").manual_seed(0)
+        for M, K, N in ((1000, 191, 128), (257, 63, 128), (4099, 128, 3), (130, 37, 128), (64, 155, 64), (5, 128, 1),
+                        (20000, 128, 128), (333, 16, 24)):
+            Xb = torch.randn((M, K + 5), generator=g).to(DEV)
+            W = torch.randn((N, K + 3), generator=g).to(DEV)
+            b = torch.randn((N,), generator=g).to(DEV)
+            X, Wv = Xb[:, 2:2 + K], W[:, 1:1 + K]
+            Yb = torch.zeros((M, N + 2), device=DEV)
+            Y = Yb[:, 1:1 + N]
+            ops.linear_fwd(X, Wv, b, Y)
+            ref = X.double() @ Wv.double().t() + b.double()
+            assert rel_err(Y.cpu().numpy(), ref.cpu().numpy()) <= tol, (M, K, N)
+            assert float(Yb[:, 0].abs().max()) == 0.0 and float(Yb[:, N + 1].abs().max()) == 0.0
+            ops.linear_fwd(X, Wv, None, Y, accumulate=True, relu=True)
+            ref2 = torch.relu(ref + X.double() @ Wv.double().t())
+            assert rel_err(Y.cpu().numpy(), ref2.cpu().numpy()) <= tol, (M, K, N)
+            dY = torch.randn((M, N), generator=g).to(DEV)
+            dX = torch.full((M, K), 7.0, device=DEV)
+            ops.linear_bwd_input(dY, Wv, dX)
+            assert rel_err(dX.cpu().numpy(), (dY.double() @ Wv.double()).cpu().numpy()) <= tol, (M, K, N)
+            ops.linear_bwd_input(dY, Wv, dX, accumulate=True)
+            assert rel_err(dX.cpu().numpy(), (2 * dY.double() @ Wv.double()).cpu().numpy()) <= tol, (M, K, N)
+            dWb, db = torch.zeros((N, K + 3), device=DEV), torch.zeros((N,), device=DEV)
+            ops.linear_bwd_weight(dY, X, dWb[:, 1:1 + K], db)
+            assert rel_err(dWb[:, 1:1 + K].cpu().numpy(), (dY.double().t() @ X.double()).cpu().numpy()) <= tol, (M, K, N)
+            assert rel_err(db.cpu().numpy(), dY.double().sum(0).cpu().numpy()) <= 1e-5
+            assert float(dWb[:, 0].abs().max()) == 0.0 and float(dWb[:, 1 + K:].abs().max()) == 0.0
+    finally:
+        L.check(L.load().ucn_train_gemm_mode(0))
 
 
 @pytest.mark.parametrize("name", GRAD_CASES)
@@ -91,8 +112,9 @@ def test_composite_backward(name):
 
 
 @pytest.mark.parametrize("name", GRAD_CASES)
-def test_mlp_train_primitives(name):
+def test_mlp_train_primitives(name, gemm):
     """K3b: forward with saved activations + backward on the CUDA primitives vs the reference's autograd gradients."""
+    TOL = gemm
     from ucnerf_b200 import train_path as TP
     c = load_grad_case(name)
     g = c["gg"]
@@ -100,7 +122,9 @@ def test_mlp_train_primitives(name):
     R, S, F = feat.shape
     P = {n: T(c["weights"]["nerf." + n]) for n in TP.PARAM_NAMES}
     raw, saved = TP.mlp_forward_train(TP.CudaOps(), P, T(r["ndc"]["ndc"].reshape(-1, 3)), T(ang), T(feat.reshape(-1, F)), S)
-    assert np.abs(raw.cpu().numpy().reshape(R, S, 4) - c["g"]["raw"][:R]).max() <= 1e-4
+    got, want = raw.cpu().numpy().reshape(R, S, 4), c["g"]["raw"][:R]
+    assert np.abs(got[..., :3] - want[..., :3]).max() <= 1e-4          # rgb in (0, 1): absolute
+    assert rel_err(got[..., 3], want[..., 3]) <= 1e-4                   # sigma is unbounded: relative to its largest value
     G = {n: torch.zeros_like(p) for n, p in P.items()}
     d_feat = TP.mlp_backward(TP.CudaOps(), P, saved, T(g["d_raw"].reshape(-1, 4)), G)
     assert rel_err(d_feat.cpu().numpy().reshape(R, S, F), g["d_feat"]) <= TOL
@@ -132,9 +156,10 @@ def test_gather_backward(name):
 
 
 @pytest.mark.parametrize("name", GRAD_CASES)
-def test_drop_in_training_step_gradients(name):
+def test_drop_in_training_step_gradients(name, gemm):
     """The reference's training-step graph (train.py:147-190) on the drop-in API: build rays, `rendering` with
     autograd, loss, backward -- every gradient the reference produces, same tensors, same shapes."""
+    TOL = gemm
     from test_gpu_parity import make_model, make_query, ref_inputs
     from ucnerf_b200 import rays, renderer
     c = load_grad_case(name)

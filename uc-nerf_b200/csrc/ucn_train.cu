@@ -6,10 +6,14 @@
 // uc-nerf_b200/train_path.py; every tensor is row-major fp32 with an explicit leading dimension, weights and their
 // gradients stay in the reference's own [out][in] layout, so parameter .grad buffers are written in place.
 //
-// First cut, correctness before speed: one generic SIMT fp32 GEMM (64x64 tile, 4x4 micro-tile, strided operands,
-// optional split of the reduction dimension with atomic accumulation) serves the three nn.Linear products.  The
-// training batch is 2 048 rays (258 K samples, ~0.2 TFLOP per step), two orders of magnitude below a rendered frame.
+// The three nn.Linear products (forward, grad-input, grad-weight) are one strided GEMM  C[i][j] = sum_p A(i,p) B(p,j)
+// with two implementations: gemm_tc_kernel (tcgen05, split-bf16 operands converted on the fly, fp32 accumulation in
+// TMEM) for every product that fills a 128-wide tile, and gemm_kernel (fp32 CUDA cores) for the 3- and 1-wide heads.
+// The training batch is 2 048 rays (258 K samples, ~0.2 TFLOP per step), two orders of magnitude below a rendered frame.
 #include "ucn_common.cuh"
+#include "ucn_tc.cuh"
+
+using namespace ucn_tc;
 
 namespace {
 
@@ -68,6 +72,269 @@ gemm_kernel(const float *__restrict__ A, long long sai, long long sap, const flo
   }
 }
 
+
+// ---- the same product on the tensor cores ---------------------------------------------------------------------------
+// C tile 128 x 128 per CTA, fp32 operands converted on the fly to THREE bf16 parts (a = a1 + a2 + a3, 24 significant
+// bits) and multiplied with the six tcgen05.mma whose terms are >= 2^-24 relative (a1b1, a1b2, a2b1, a1b3, a2b2, a3b1),
+// fp32 accumulation in TMEM: fp32-class products on the tensor cores.  The two-part split of the inference kernel
+// (~16 bits, 5e-6 per product) is not enough here: its 1.7e-4 forward error flips ReLU masks of near-zero units and a
+// flipped mask changes a gradient sum by a whole term (measured 2.6e-3 of a weight gradient on 3 072 samples).  The
+// tensor pipe has the headroom: this kernel is bound by operand staging, not by MMA issue.  The 256 threads
+// stage a [128 x 32] slab of each operand per iteration straight from global memory (any strides: the three nn.Linear
+// products differ only in which index is contiguous) into the UMMA no-swizzle K-major core-matrix layout
+// (element (row, k) at (k/8)*2048 + row*16 + (k%8)*2 bytes), two stages deep: the six MMAs of slab t run while slab
+// t+1 is being converted.  Epilogue: TMEM -> registers -> bias / accumulate / ReLU -> global, or fp32 atomics when the
+// reduction dimension is split across CTAs (grad-weight).
+constexpr int TC_SLAB = 32;                       // reduction elements per stage (two K=16 MMA steps)
+constexpr uint32_t TC_CHUNK = 2048;               // one K-chunk (8 bf16) x 128 rows
+constexpr int TC_PARTS = 3;                       // bf16 parts per fp32 operand (8 + 8 + 8 significant bits)
+constexpr uint32_t TC_PART = 4 * TC_CHUNK;        // one part of one operand slab: 4 K-chunks = 8 KB
+constexpr uint32_t TC_OPER = TC_PARTS * TC_PART;  // all parts of one operand slab = 24 KB
+constexpr uint32_t TC_STAGE = 2 * TC_OPER;        // A + B
+constexpr uint32_t TC_SMEM = 2 * TC_STAGE + 64;
+
+// (a, b) -> three packed bf16 pairs: rounded values, rounded first residuals, rounded second residuals
+__device__ __forceinline__ void split3(float a, float b, uint32_t (&w)[3]) {
+  w[0] = pack2(a, b);
+  const float ra = a - bf_lo(w[0]), rb = b - bf_hi(w[0]);
+  w[1] = pack2(ra, rb);
+  w[2] = pack2(ra - bf_lo(w[1]), rb - bf_hi(w[1]));
+}
+
+__global__ void __launch_bounds__(256)
+gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const float *__restrict__ B, long long sbp,
+               long long sbj, float *__restrict__ C, long long ldc, const float *__restrict__ bias, int I, int J,
+               long long P, long long p_chunk, int flags, int a_vec, int b_vec) {
+  extern __shared__ __align__(1024) unsigned char tc_smem[];
+  const uint32_t sbase = smem_u32(tc_smem);
+  const uint32_t bar_done = sbase + 2 * TC_STAGE, tmem_slot = bar_done + 16;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int i0 = blockIdx.x * 128, j0 = blockIdx.y * 128;
+  const long long p_begin = (long long)blockIdx.z * p_chunk, p_end = min(P, p_begin + p_chunk);
+  if (tid == 0) {
+    mbar_init(bar_done, 1); mbar_init(bar_done + 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(tc_smem + 2 * TC_STAGE + 16);
+  const uint32_t idesc = umma_idesc_bf16(128);
+  const int row = tid & 127, half = tid >> 7;                 // this thread stages k = 16*half .. 16*half+15 of its row
+  const bool a_ok = i0 + row < I, b_ok = j0 + row < J;
+  const int n_iter = (int)((p_end - p_begin + TC_SLAB - 1) / TC_SLAB);
+  for (int it = 0; it < n_iter; ++it) {
+    const int st = it & 1;
+    const long long ps = p_begin + (long long)it * TC_SLAB, p0 = ps + 16 * half;
+    // Operand slabs [128 rows x 32 p].  Two staging patterns per operand:
+    //   vec    (p contiguous, 16-byte aligned rows): lanes sweep p, one float4 per lane -> four full 128-byte lines per
+    //          warp instruction;
+    //   scalar (rows contiguous, or unaligned): thread = row, 16 p values each -- coalesced when the row index is the
+    //          contiguous one (grad-weight operands, grad-input weights), L1-cached otherwise (small weight matrices).
+    float va[16], vb[16];
+    float4 fa[4], fb[4];
+    if (a_vec) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int f = tid + 256 * q, r = f >> 3, c4 = f & 7;
+        const long long pp = ps + 4 * c4;
+        fa[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i0 + r < I && pp < p_end) {
+          fa[q] = *reinterpret_cast<const float4 *>(A + (long long)(i0 + r) * sai + pp);
+          if (pp + 1 >= p_end) fa[q].y = 0.f;
+          if (pp + 2 >= p_end) fa[q].z = 0.f;
+          if (pp + 3 >= p_end) fa[q].w = 0.f;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 16; ++k) va[k] = (a_ok && p0 + k < p_end) ? A[(long long)(i0 + row) * sai + (p0 + k) * sap] : 0.0f;
+    }
+    if (b_vec) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int f = tid + 256 * q, r = f >> 3, c4 = f & 7;
+        const long long pp = ps + 4 * c4;
+        fb[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (j0 + r < J && pp < p_end) {
+          fb[q] = *reinterpret_cast<const float4 *>(B + (long long)(j0 + r) * sbj + pp);
+          if (pp + 1 >= p_end) fb[q].y = 0.f;
+          if (pp + 2 >= p_end) fb[q].z = 0.f;
+          if (pp + 3 >= p_end) fb[q].w = 0.f;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 16; ++k) vb[k] = (b_ok && p0 + k < p_end) ? B[(p0 + k) * sbp + (long long)(j0 + row) * sbj] : 0.0f;
+    }
+    if (it >= 2) mbar_wait(bar_done + 8 * st, (uint32_t)(((it >> 1) - 1) & 1));     // MMAs of slab it-2 have read this stage
+    const uint32_t stage = sbase + st * TC_STAGE;
+#pragma unroll
+    for (int op = 0; op < 2; ++op) {
+      const uint32_t base = stage + op * TC_OPER;
+      if (op == 0 ? a_vec : b_vec) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int f = tid + 256 * q, r = f >> 3, c4 = f & 7;
+          const float4 v = op == 0 ? fa[q] : fb[q];
+          uint32_t w0[3], w1[3];
+          split3(v.x, v.y, w0);
+          split3(v.z, v.w, w1);
+          const uint32_t addr = base + (c4 >> 1) * TC_CHUNK + r * 16 + (c4 & 1) * 8;
+#pragma unroll
+          for (int pt = 0; pt < TC_PARTS; ++pt)
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr + pt * TC_PART), "r"(w0[pt]), "r"(w1[pt]) : "memory");
+        }
+      } else {
+        const float *v = op == 0 ? va : vb;
+        const uint32_t sa = base + row * 16 + (2 * half) * TC_CHUNK;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t w[4][3];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) split3(v[8 * c + 2 * q], v[8 * c + 2 * q + 1], w[q]);
+#pragma unroll
+          for (int pt = 0; pt < TC_PARTS; ++pt) sts128(sa + c * TC_CHUNK + pt * TC_PART, w[0][pt], w[1][pt], w[2][pt], w[3][pt]);
+        }
+      }
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint32_t a0 = sbase + st * TC_STAGE, b0 = a0 + TC_OPER;
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        uint64_t da[TC_PARTS], db[TC_PARTS];
+#pragma unroll
+        for (int pt = 0; pt < TC_PARTS; ++pt) {
+          da[pt] = umma_desc(a0 + pt * TC_PART + u * 2 * TC_CHUNK, TC_CHUNK, 128);
+          db[pt] = umma_desc(b0 + pt * TC_PART + u * 2 * TC_CHUNK, TC_CHUNK, 128);
+        }
+        umma_ss(tmem_base, da[0], db[0], idesc, (it > 0 || u > 0) ? 1u : 0u);
+        umma_ss(tmem_base, da[0], db[1], idesc, 1u);
+        umma_ss(tmem_base, da[1], db[0], idesc, 1u);
+        umma_ss(tmem_base, da[0], db[2], idesc, 1u);
+        umma_ss(tmem_base, da[1], db[1], idesc, 1u);
+        umma_ss(tmem_base, da[2], db[0], idesc, 1u);
+      }
+      umma_commit(bar_done + 8 * st);
+    }
+  }
+  {
+    const int last = n_iter - 1;
+    mbar_wait(bar_done + 8 * (last & 1), (uint32_t)((last >> 1) & 1));
+    tc_fence_after();
+  }
+  // ---- epilogue: warp w reads TMEM lanes 32*(w%4).., columns 64*(w/4).. (thread = row), transposes 32 x 32 blocks
+  // through shared memory (the operand stages are free: every MMA has completed) and writes each output row segment
+  // as one coalesced 128-byte store / atomic ---------------------------------------------------------------------------
+  {
+    const int q = warp & 3, hf = warp >> 2;
+    const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + 64 * hf;
+    float *tile = reinterpret_cast<float *>(tc_smem) + warp * (32 * 33);
+#pragma unroll 1
+    for (int c0 = 0; c0 < 64; c0 += 32) {
+      uint32_t acc[32];
+      tmem_ld32(taddr + c0, acc);
+      tmem_wait_ld();
+#pragma unroll
+      for (int c = 0; c < 32; ++c) tile[lane * 33 + c] = __uint_as_float(acc[c]);
+      __syncwarp();
+      const int j = j0 + 64 * hf + c0 + lane;
+      const float bj = (bias && j < J && !(flags & G_ATOMIC)) ? bias[j] : 0.0f;
+      if (j < J) {
+#pragma unroll 4
+        for (int r = 0; r < 32; ++r) {
+          const int i = i0 + 32 * q + r;
+          if (i >= I) break;
+          float v = tile[r * 33 + lane];
+          float *dst = C + (long long)i * ldc + j;
+          if (flags & G_ATOMIC) { atomicAdd(dst, v); continue; }
+          v += bj;
+          if (flags & G_ACCUM) v += *dst;
+          if (flags & G_RELU) v = fmaxf(v, 0.0f);
+          *dst = v;
+        }
+      }
+      __syncwarp();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+  }
+}
+
+
+// ---- the 3- and 1-wide heads (confi_rgb / alpha_1 / rgb / alpha, network/models.py:161-162,170,174) ------------------
+// A 64- or 128-wide GEMM tile would be >95 % padding there; these three kernels stream the wide operand once, coalesced.
+// forward: warp per row, lanes over k, shuffle reduction.  Y[m][n] (+)= sum_k X[m][k] W[n][k] + b[n], N <= 4
+__global__ void __launch_bounds__(256)
+skinny_fwd_kernel(const float *__restrict__ X, long long ldx, const float *__restrict__ W, long long ldw,
+                  const float *__restrict__ b, long long M, int K, int N, float *__restrict__ Y, long long ldy, int flags) {
+  const int lane = threadIdx.x & 31;
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (m >= M) return;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int k = lane; k < K; k += 32) {
+    const float x = X[m * ldx + k];
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+      if (n < N) acc[n] = fmaf(x, W[n * ldw + k], acc[n]);
+  }
+#pragma unroll
+  for (int n = 0; n < 4; ++n)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], o);
+  if (lane < N) {
+    float v = lane == 0 ? acc[0] : (lane == 1 ? acc[1] : (lane == 2 ? acc[2] : acc[3]));
+    if (b) v += b[lane];
+    float *dst = Y + m * ldy + lane;
+    if (flags & G_ACCUM) v += *dst;
+    if (flags & G_RELU) v = fmaxf(v, 0.0f);
+    *dst = v;
+  }
+}
+// grad-input: dX[m][k] (+)= sum_{n<N} dY[m][n] W[n][k], N <= 4 (thread per output element)
+__global__ void __launch_bounds__(256)
+skinny_bwd_input_kernel(const float *__restrict__ dY, long long ldy, const float *__restrict__ W, long long ldw,
+                        long long M, int K, int N, float *__restrict__ dX, long long ldx, int flags) {
+  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= M * K) return;
+  const long long m = e / K;
+  const int k = (int)(e - m * K);
+  float v = 0.f;
+  for (int n = 0; n < N; ++n) v = fmaf(dY[m * ldy + n], W[n * ldw + k], v);
+  float *dst = dX + m * ldx + k;
+  *dst = (flags & G_ACCUM) ? *dst + v : v;
+}
+// grad-weight: dW[n][k] += sum_m dY[m][n] X[m][k], N <= 4: thread = k, block = one chunk of rows, atomics at the end
+__global__ void __launch_bounds__(128)
+skinny_bwd_weight_kernel(const float *__restrict__ dY, long long ldy, const float *__restrict__ X, long long ldx,
+                         long long M, int K, int N, long long m_chunk, float *dW, long long lddw) {
+  const int k = blockIdx.y * 128 + threadIdx.x;
+  if (k >= K) return;
+  const long long m0 = (long long)blockIdx.x * m_chunk, m1 = min(M, m0 + m_chunk);
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (long long m = m0; m < m1; ++m) {
+    const float x = X[m * ldx + k];
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+      if (n < N) acc[n] = fmaf(dY[m * ldy + n], x, acc[n]);
+  }
+  for (int n = 0; n < N; ++n) atomicAdd(dW + n * lddw + k, acc[n]);
+}
+
+int g_gemm_mode = 0;     // 0: tensor cores where the shape fills a tile, 1: SIMT fp32 only
+
 // db[n] += sum_m dY[m][n]
 __global__ void __launch_bounds__(256)
 colsum_kernel(const float *__restrict__ dY, long long ldy, long long M, int Nn, long long m_chunk, float *db) {
@@ -123,7 +390,7 @@ __global__ void film_relu_bwd_kernel(const float *__restrict__ dh, long long ldd
   if (e >= M * 128) return;
   const long long m = e >> 7;
   const int c = (int)(e & 127);
-  const float g = h[m * ldh + c] > 0.0f ? dh[m * lddh + c] : 0.0f;
+  const float g = pre[e] * mod[e] > 0.0f ? dh[m * lddh + c] : 0.0f;      // == h > 0 (h = relu(pre * mod)): h is not re-read
   dpre[e] = g * mod[e];
   const float dm = g * pre[e];
   dmod[e] = accumulate ? dmod[e] + dm : dm;
@@ -186,15 +453,33 @@ int launch_gemm(const float *A, long long sai, long long sap, const float *B, lo
                 long long ldc, const float *bias, long long I, long long J, long long P, int flags, int splits,
                 void *stream) {
   if (I <= 0 || J <= 0) return UCN_OK;
+  // heads (3 / 1 outputs) and tiny reductions stay on the CUDA cores: a 128 x 128 tensor-core tile would be padding
+  const bool tc = g_gemm_mode == 0 && I >= 64 && J >= 16 && P >= 16;
+  const int tile = tc ? 128 : BT, pstep = tc ? TC_SLAB : PT;
   long long p_chunk = P;
   if (splits > 1) {
-    p_chunk = ((P + splits - 1) / splits + PT - 1) / PT * PT;
+    p_chunk = ((P + splits - 1) / splits + pstep - 1) / pstep * pstep;
     splits = (int)((P + p_chunk - 1) / p_chunk);
   } else {
     splits = 1;
   }
-  dim3 grid(nblk(I, BT), nblk(J, BT), (unsigned)splits);
+  dim3 grid(nblk(I, tile), nblk(J, tile), (unsigned)splits);
   UCN_CHECK_ARG(grid.y < 65536u, "ucn_linear: output too wide");
+  if (tc) {
+    static bool attr = false;
+    if (!attr) {
+      cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM);
+      if (e != cudaSuccess) return ucn_cuda_status(e, "gemm_tc smem attribute");
+      attr = true;
+    }
+    // float4 staging needs p contiguous, 16-byte aligned rows, and the last (partial) float4 of a row inside its pitch
+    const long long P4 = (P + 3) & ~3ll;
+    const int a_vec = sap == 1 && splits == 1 && (reinterpret_cast<uintptr_t>(A) & 15) == 0 && (sai & 3) == 0 && P4 <= sai;
+    const int b_vec = sbp == 1 && splits == 1 && (reinterpret_cast<uintptr_t>(B) & 15) == 0 && (sbj & 3) == 0 && P4 <= sbj;
+    gemm_tc_kernel<<<grid, 256, TC_SMEM, (cudaStream_t)stream>>>(A, sai, sap, B, sbp, sbj, C, ldc, bias, (int)I, (int)J, P, p_chunk, flags, a_vec, b_vec);
+    UCN_LAUNCH_CHECK("gemm_tc_kernel");
+    return UCN_OK;
+  }
   gemm_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(A, sai, sap, B, sbp, sbj, C, ldc, bias, (int)I, (int)J, P, p_chunk, flags);
   UCN_LAUNCH_CHECK("gemm_kernel");
   return UCN_OK;
@@ -202,11 +487,22 @@ int launch_gemm(const float *A, long long sai, long long sap, const float *B, lo
 
 }  // namespace
 
+// 0: nn.Linear products on tcgen05 (split-bf16, fp32 accumulate) where the shape fills a tile; 1: fp32 CUDA cores only
+extern "C" int ucn_train_gemm_mode(int mode) {
+  UCN_CHECK_ARG(mode == 0 || mode == 1, "ucn_train_gemm_mode: 0 (tensor cores) or 1 (SIMT fp32)");
+  g_gemm_mode = mode;
+  return UCN_OK;
+}
 // Y[m][n] (+)= sum_k X[m*ldx + k] W[n*ldw + k] + b[n]     (nn.Linear forward; b may be NULL; flags: 1 accumulate, 2 ReLU)
 extern "C" int ucn_linear_fwd(const float *X, int64_t ldx, const float *W, int64_t ldw, const float *b, int64_t M, int K,
                               int N, float *Y, int64_t ldy, int flags, void *stream) {
   UCN_CHECK_ARG(X && W && Y, "ucn_linear_fwd: null argument");
   UCN_CHECK_ARG((flags & ~3) == 0, "ucn_linear_fwd: flags");
+  if (N <= 4 && M > 0) {
+    skinny_fwd_kernel<<<nblk(M, 8), 256, 0, (cudaStream_t)stream>>>(X, ldx, W, ldw, b, M, K, N, Y, ldy, flags);
+    UCN_LAUNCH_CHECK("skinny_fwd_kernel");
+    return UCN_OK;
+  }
   return launch_gemm(X, ldx, 1, W, 1, ldw, Y, ldy, b, M, N, K, flags, 1, stream);
 }
 // dX[m][k] (+)= sum_n dY[m*ldy + n] W[n*ldw + k]           (nn.Linear grad-input; flags: 1 accumulate)
@@ -214,6 +510,11 @@ extern "C" int ucn_linear_bwd_input(const float *dY, int64_t ldy, const float *W
                                     float *dX, int64_t ldx, int flags, void *stream) {
   UCN_CHECK_ARG(dY && W && dX, "ucn_linear_bwd_input: null argument");
   UCN_CHECK_ARG((flags & ~1) == 0, "ucn_linear_bwd_input: flags");
+  if (N <= 4 && M > 0) {
+    skinny_bwd_input_kernel<<<nblk(M * K, 256), 256, 0, (cudaStream_t)stream>>>(dY, ldy, W, ldw, M, K, N, dX, ldx, flags);
+    UCN_LAUNCH_CHECK("skinny_bwd_input_kernel");
+    return UCN_OK;
+  }
   return launch_gemm(dY, ldy, 1, W, ldw, 1, dX, ldx, nullptr, M, K, N, flags, 1, stream);
 }
 // dW[n*lddw + k] += sum_m dY[m*ldy + n] X[m*ldx + k],  db[n] += sum_m dY[m*ldy + n]   (grad-weight; db may be NULL)
@@ -221,14 +522,25 @@ extern "C" int ucn_linear_bwd_weight(const float *dY, int64_t ldy, const float *
                                      float *dW, int64_t lddw, float *db, void *stream) {
   UCN_CHECK_ARG(dY && X && dW, "ucn_linear_bwd_weight: null argument");
   if (M <= 0) return UCN_OK;
-  const long long tiles = (long long)((N + BT - 1) / BT) * ((K + BT - 1) / BT);
+  if (N <= 4) {
+    skinny_bwd_weight_kernel<<<dim3(nblk(M, 256), nblk(K, 128)), 128, 0, (cudaStream_t)stream>>>(dY, ldy, X, ldx, M, K, N, 256, dW, lddw);
+    UCN_LAUNCH_CHECK("skinny_bwd_weight_kernel");
+    if (db) {
+      colsum_kernel<<<dim3(nblk(N, 32), nblk(M, 512)), 256, 0, (cudaStream_t)stream>>>(dY, ldy, M, N, 512, db);
+      UCN_LAUNCH_CHECK("colsum_kernel");
+    }
+    return UCN_OK;
+  }
+  const bool tc = g_gemm_mode == 0 && N >= 64 && K >= 16 && M >= 16;
+  const int tile = tc ? 128 : BT;
+  const long long tiles = (long long)((N + tile - 1) / tile) * ((K + tile - 1) / tile);
   int splits = (int)((2 * 148 + tiles - 1) / tiles);
-  const long long max_splits = (M + 4 * PT - 1) / (4 * PT);
+  const long long max_splits = (M + 255) / 256;
   if (splits > max_splits) splits = (int)max_splits;
   const int rc = launch_gemm(dY, 1, ldy, X, ldx, 1, dW, lddw, nullptr, N, K, M, G_ATOMIC, splits < 1 ? 1 : splits, stream);
   if (rc != UCN_OK || !db) return rc;
-  const long long chunks = (M + 4095) / 4096;
-  colsum_kernel<<<dim3(nblk(N, 32), (unsigned)chunks), 256, 0, (cudaStream_t)stream>>>(dY, ldy, M, N, 4096, db);
+  const long long chunks = (M + 511) / 512;
+  colsum_kernel<<<dim3(nblk(N, 32), (unsigned)chunks), 256, 0, (cudaStream_t)stream>>>(dY, ldy, M, N, 512, db);
   UCN_LAUNCH_CHECK("colsum_kernel");
   return UCN_OK;
 }

@@ -71,6 +71,7 @@ _SIGS = {
     "ucn_composite": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, _fp]),
     "ucn_composite_bwd": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp]),
     "ucn_gather_bwd": (C.c_int, [C.POINTER(Frame), _fp, _fp, _fp, _fp, C.c_int64, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "ucn_train_gemm_mode": (C.c_int, [C.c_int]),
     "ucn_linear_fwd": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, _fp, C.c_int64, C.c_int, C.c_int, _fp, C.c_int64,
                                  C.c_int, _fp]),
     "ucn_linear_bwd_input": (C.c_int, [_fp, C.c_int64, _fp, C.c_int64, C.c_int64, C.c_int, C.c_int, _fp, C.c_int64,
