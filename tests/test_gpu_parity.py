@@ -41,7 +41,7 @@ def make_model(c, mode):
     m = models.UCNeRF(D=6, W=128, input_ch_pts=63, skips=[4], input_ch_views=27, input_ch_feat=c["scene"].feat_dim,
                       view_num=c["V"] + 1, mode=mode)
     m.load_state_dict({k: torch.from_numpy(v) for k, v in c["weights"].items()})
-    return m.to(DEV)
+    return m.to(DEV).eval()          # eval loop (train.py:251-279); the training path needs train() (tests/test_gpu_grad.py)
 
 
 def make_query(mode="fp32"):

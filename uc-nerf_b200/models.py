@@ -6,8 +6,8 @@
 ``UCNeRF`` keeps the reference's parameter names and shapes (``state_dict()`` keys ``nerf.*``, including the
 three layers forward() never uses, Q9) so released ``.tar`` checkpoints load unchanged; ``forward`` runs
 the fused CUDA kernel (PE + 13 linear layers + FiLM + uncertainty blend) -- fp32 SIMT (`mode='fp32'`) or
-bf16 tcgen05 (`mode='bf16'`).  When autograd is recording and a parameter or the feature rows require grad (the
-training step, train.py:147-190), ``forward_fused`` switches to the fp32 training primitives and their backward
+bf16 tcgen05 (`mode='bf16'`).  In train() mode, when autograd is recording and a parameter or the feature rows require
+grad (the training step, train.py:147-190), ``forward_fused`` switches to the fp32 training primitives and their backward
 (train_path.MlpFn).
 """
 from __future__ import annotations
@@ -141,8 +141,10 @@ class UCNeRF(nn.Module):
     def forward_fused(self, ndc_pts, viewdirs, feats, mode: Optional[str] = None):
         """ndc_pts [R,S,3], viewdirs [R,3] (per ray), feats [R,S,F] -> raw [R,S,4] = (rgb, sigma)."""
         R, S = feats.shape[:2]
-        if _tp.wants_grad(feats, *self.parameters()):
-            # training step (train.py:147-190): fp32 primitives with saved activations + their backward (K3b)
+        if self.training and _tp.wants_grad(feats, *self.parameters()):
+            # training step (train.py:147-190): primitives with saved activations + their backward (K3b).  Only in
+            # train() mode: the eval loop (train.py:251-279, Lightning's validation: eval() + no_grad) renders whole
+            # frames, whose saved activations (9.6 KB per sample) would not fit.
             named = dict(self.nerf.named_parameters())
             return _tp.MlpFn.apply(ndc_pts, viewdirs, feats, S, *[named[n] for n in _tp.PARAM_NAMES])
         pw = self.packed()
