@@ -174,7 +174,17 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on fd 1 when the communicator is created: stdout carries the JSON line only
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
     L.check(L.load().ucn_check_device(), "ucn_check_device")
 
     H, W, V, S = wl["H"], wl["W"], wl["V"], wl["S"]
