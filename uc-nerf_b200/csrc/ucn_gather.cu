@@ -63,19 +63,21 @@ __device__ __forceinline__ void tri8(const float *__restrict__ vol, int D, int h
   for (int c = 0; c < 8; ++c) out[c * os] = a.v[c];
 }
 
-template <bool FROM_Z>
-__global__ void __launch_bounds__(kThreads)
+template <bool FROM_Z, bool TILED>
+__global__ void __launch_bounds__(kThreads, TILED ? 8 : 7)
 gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts_or_z,
               const float *__restrict__ ndc1, const float *__restrict__ ndc2, const float *__restrict__ ndc3,
-              const float *__restrict__ pix_yx, int ray0, int R, int64_t n_samples, int parts, int tiled,
+              const float *__restrict__ pix_yx, int ray0, int R, int64_t n_samples, int parts,
               float *__restrict__ feat, float *__restrict__ ndc_out, int32_t *__restrict__ idx_out) {
   extern __shared__ float rows[];                       // [kThreads][F + 1]  (+1: odd stride, no bank conflicts)
   const int V = f.V, F = 24 + 12 * V + 1, ld = F + 1;
   const int64_t q = (int64_t)blockIdx.x * kThreads + threadIdx.x;
   // channel c of this sample goes to row[c * os]: shared-memory staging row, or (tiled) straight to the
   // [F][128] tile of this block in global memory
-  const int os = tiled ? kThreads : 1;
-  float *row = tiled ? feat + (int64_t)blockIdx.x * F * kThreads + threadIdx.x : rows + (size_t)threadIdx.x * ld;
+  // (TILED is a template parameter so that the 61 channel stores compile to STG / STS instead of generic ST, and the
+  //  tiled instance, which needs no shared memory, is held to 64 registers: 8 blocks per SM instead of 7)
+  constexpr int os = TILED ? kThreads : 1;
+  float *row = TILED ? feat + (int64_t)blockIdx.x * F * kThreads + threadIdx.x : rows + (size_t)threadIdx.x * ld;
   if (q < n_samples) {
     const float iw = (float)(f.W - 1), ih = (float)(f.H - 1);
     float p[3], c1[3], c2[3], c3[3];
@@ -157,7 +159,7 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
       if (ir) { ir[11 + 3 * v] = ax.i0; ir[12 + 3 * v] = ay.i0; ir[13 + 3 * v] = (int32_t)m; }
     }
   }
-  if (tiled) {
+  if (TILED) {
     // tile-transposed rows for the tensor-core MLP: block == one 128-sample tile, laid out [F][128] so that both
     // the stores above and the MLP's per-row loads are one coalesced 128-byte line per warp and channel
     if (q >= n_samples)
@@ -187,17 +189,21 @@ static int launch_gather(bool from_z, const ucn_frame *f, const float *a, const 
   const int F = 24 + 12 * f->V + 1;
   const size_t smem = tiled ? 0 : (size_t)kThreads * (F + 1) * sizeof(float);
   const unsigned blocks = (unsigned)((n + kThreads - 1) / kThreads);
-  if (from_z) {
-    static bool attr = false;
-    if (!attr) { cudaFuncSetAttribute(gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; }
-    gather_kernel<true><<<blocks, kThreads, smem, (cudaStream_t)stream>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts,
-                                                                         tiled, feat, ndc_out, idx);
-  } else {
-    static bool attr = false;
-    if (!attr) { cudaFuncSetAttribute(gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; }
-    gather_kernel<false><<<blocks, kThreads, smem, (cudaStream_t)stream>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts,
-                                                                          tiled, feat, ndc_out, idx);
+  const cudaStream_t st = (cudaStream_t)stream;
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(gather_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(gather_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    attr = true;
   }
+  if (from_z && tiled)
+    gather_kernel<true, true><<<blocks, kThreads, 0, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
+  else if (from_z)
+    gather_kernel<true, false><<<blocks, kThreads, smem, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
+  else if (tiled)
+    gather_kernel<false, true><<<blocks, kThreads, 0, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
+  else
+    gather_kernel<false, false><<<blocks, kThreads, smem, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
   UCN_LAUNCH_CHECK("gather_kernel");
   return UCN_OK;
 }
