@@ -213,10 +213,12 @@ int ucn_linear_bwd_weight(const float *dY, int64_t ldy, const float *X, int64_t 
 /* ph[:, 0:63] = PE_10(ndc [N][3]); ftv[:, 128:155] = PE_4(angle[ray]) (network/models.py:50-54, renderer.py:88-100) */
 int ucn_train_prep(const float *ndc, const float *angle, int S, int64_t N, float *ph, int64_t ldph, float *ftv,
                    int64_t ldftv, void *stream);
-/* h = relu(pre * mod) over [M][128] (network/models.py:154-155) and its backward (dmod optionally accumulated) */
+/* h = relu(pre * mod) over [M][128] (network/models.py:154-155) */
 int ucn_film_relu_fwd(const float *pre, const float *mod, float *h, int64_t ldh, int64_t M, void *stream);
-int ucn_film_relu_bwd(const float *dh, int64_t lddh, const float *pre, const float *mod, const float *h, int64_t ldh,
-                      float *dpre, float *dmod, int accumulate, int64_t M, void *stream);
+/* backward: dpre = dh * mod * [pre*mod > 0], dmod (+)= dh * pre * [pre*mod > 0]; db (optional) += column sums of dpre
+ * (the bias gradient of the layer that produced pre) */
+int ucn_film_relu_bwd(const float *dh, int64_t lddh, const float *pre, const float *mod, float *dpre, float *dmod,
+                      int accumulate, float *db, int64_t M, void *stream);
 /* o = a * b over [M][128] (h * feats_bias, network/models.py:164); backward: da (+)= do*b, db = do*a */
 int ucn_mul_fwd(const float *a, int64_t lda, const float *b, float *o, int64_t M, void *stream);
 int ucn_mul_bwd(const float *d_o, const float *a, int64_t lda, const float *b, float *da, int accumulate, float *db,

@@ -52,11 +52,13 @@ class OracleOps:
     def film_relu_fwd(self, PRE, MOD, H):
         _n(H)[...] = np.maximum(_n(PRE) * _n(MOD), np.float32(0))
 
-    def film_relu_bwd(self, dH, PRE, MOD, H, dPRE, dMOD, accumulate):
-        g = np.where(_n(H) > 0, _n(dH), np.float32(0))
+    def film_relu_bwd(self, dH, PRE, MOD, dPRE, dMOD, accumulate, db):
+        g = np.where(_n(PRE) * _n(MOD) > 0, _n(dH), np.float32(0))
         _n(dPRE)[...] = g * _n(MOD)
         dm = g * _n(PRE)
         _n(dMOD)[...] = _n(dMOD) + dm if accumulate else dm
+        if db is not None:
+            _n(db)[...] += _n(dPRE).astype(np.float64).sum(0).astype(np.float32)
 
     def mul_fwd(self, A, B, OUT):
         _n(OUT)[...] = _n(A) * _n(B)

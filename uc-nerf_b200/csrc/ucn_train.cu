@@ -383,17 +383,26 @@ __global__ void film_relu_fwd_kernel(const float *__restrict__ pre, const float 
   if (e >= M * 128) return;
   h[(e >> 7) * ldh + (e & 127)] = fmaxf(pre[e] * mod[e], 0.0f);
 }
-__global__ void film_relu_bwd_kernel(const float *__restrict__ dh, long long lddh, const float *__restrict__ pre,
-                                     const float *__restrict__ mod, const float *__restrict__ h, long long ldh,
-                                     float *__restrict__ dpre, float *__restrict__ dmod, int accumulate, long long M) {
-  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= M * 128) return;
-  const long long m = e >> 7;
-  const int c = (int)(e & 127);
-  const float g = pre[e] * mod[e] > 0.0f ? dh[m * lddh + c] : 0.0f;      // == h > 0 (h = relu(pre * mod)): h is not re-read
-  dpre[e] = g * mod[e];
-  const float dm = g * pre[e];
-  dmod[e] = accumulate ? dmod[e] + dm : dm;
+// thread = column, block = 64 rows: coalesced, and the bias gradient of the layer (column sums of dpre) falls out of
+// the same pass (one atomic per thread)
+__global__ void __launch_bounds__(128)
+film_relu_bwd_kernel(const float *__restrict__ dh, long long lddh, const float *__restrict__ pre,
+                     const float *__restrict__ mod, float *__restrict__ dpre, float *__restrict__ dmod, int accumulate,
+                     float *db, long long M) {
+  const int c = threadIdx.x;
+  const long long m0 = (long long)blockIdx.x * 64, m1 = min(M, m0 + 64);
+  float sum = 0.f;
+  for (long long m = m0; m < m1; ++m) {
+    const long long e = m * 128 + c;
+    const float p = pre[e], md = mod[e];
+    const float g = p * md > 0.0f ? dh[m * lddh + c] : 0.0f;      // == h > 0 (h = relu(pre * mod)): h is not re-read
+    const float dp = g * md;
+    dpre[e] = dp;
+    sum += dp;
+    const float dm = g * p;
+    dmod[e] = accumulate ? dmod[e] + dm : dm;
+  }
+  if (db) atomicAdd(db + c, sum);
 }
 __global__ void mul_fwd_kernel(const float *__restrict__ a, long long lda, const float *__restrict__ b,
                                float *__restrict__ o, long long M) {
@@ -562,11 +571,11 @@ extern "C" int ucn_film_relu_fwd(const float *pre, const float *mod, float *h, i
   UCN_LAUNCH_CHECK("film_relu_fwd_kernel");
   return UCN_OK;
 }
-extern "C" int ucn_film_relu_bwd(const float *dh, int64_t lddh, const float *pre, const float *mod, const float *h,
-                                 int64_t ldh, float *dpre, float *dmod, int accumulate, int64_t M, void *stream) {
-  UCN_CHECK_ARG(dh && pre && mod && h && dpre && dmod, "ucn_film_relu_bwd: null argument");
+extern "C" int ucn_film_relu_bwd(const float *dh, int64_t lddh, const float *pre, const float *mod, float *dpre,
+                                 float *dmod, int accumulate, float *db, int64_t M, void *stream) {
+  UCN_CHECK_ARG(dh && pre && mod && dpre && dmod, "ucn_film_relu_bwd: null argument");
   if (M <= 0) return UCN_OK;
-  film_relu_bwd_kernel<<<nblk(M * 128, 256), 256, 0, (cudaStream_t)stream>>>(dh, lddh, pre, mod, h, ldh, dpre, dmod, accumulate, M);
+  film_relu_bwd_kernel<<<nblk(M, 64), 128, 0, (cudaStream_t)stream>>>(dh, lddh, pre, mod, dpre, dmod, accumulate, db, M);
   UCN_LAUNCH_CHECK("film_relu_bwd_kernel");
   return UCN_OK;
 }

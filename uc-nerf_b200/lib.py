@@ -80,7 +80,7 @@ _SIGS = {
                                         _fp, _fp]),
     "ucn_train_prep": (C.c_int, [_fp, _fp, C.c_int, C.c_int64, _fp, C.c_int64, _fp, C.c_int64, _fp]),
     "ucn_film_relu_fwd": (C.c_int, [_fp, _fp, _fp, C.c_int64, C.c_int64, _fp]),
-    "ucn_film_relu_bwd": (C.c_int, [_fp, C.c_int64, _fp, _fp, _fp, C.c_int64, _fp, _fp, C.c_int, C.c_int64, _fp]),
+    "ucn_film_relu_bwd": (C.c_int, [_fp, C.c_int64, _fp, _fp, _fp, _fp, C.c_int, _fp, C.c_int64, _fp]),
     "ucn_mul_fwd": (C.c_int, [_fp, C.c_int64, _fp, _fp, C.c_int64, _fp]),
     "ucn_mul_bwd": (C.c_int, [_fp, _fp, C.c_int64, _fp, _fp, C.c_int, _fp, C.c_int64, _fp]),
     "ucn_relu_bwd": (C.c_int, [_fp, _fp, _fp, C.c_int64, _fp]),

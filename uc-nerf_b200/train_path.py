@@ -74,10 +74,10 @@ class CudaOps:
         h, ldh = _v(H)
         L.check(self.lib.ucn_film_relu_fwd(L.ptr(PRE), L.ptr(MOD), h, ldh, PRE.shape[0], L.stream_ptr()), "ucn_film_relu_fwd")
 
-    def film_relu_bwd(self, dH, PRE, MOD, H, dPRE, dMOD, accumulate):
-        (g, ldg), (h, ldh) = _v(dH), _v(H)
-        L.check(self.lib.ucn_film_relu_bwd(g, ldg, L.ptr(PRE), L.ptr(MOD), h, ldh, L.ptr(dPRE), L.ptr(dMOD),
-                                           int(accumulate), PRE.shape[0], L.stream_ptr()), "ucn_film_relu_bwd")
+    def film_relu_bwd(self, dH, PRE, MOD, dPRE, dMOD, accumulate, db):
+        g, ldg = _v(dH)
+        L.check(self.lib.ucn_film_relu_bwd(g, ldg, L.ptr(PRE), L.ptr(MOD), L.ptr(dPRE), L.ptr(dMOD), int(accumulate),
+                                           L.ptr(db), PRE.shape[0], L.stream_ptr()), "ucn_film_relu_bwd")
 
     def mul_fwd(self, A, B, OUT):
         a, lda = _v(A)
@@ -172,10 +172,9 @@ def mlp_backward(ops, P: Dict[str, torch.Tensor], saved, d_raw, G: Dict[str, tor
     # the six FiLM-modulated layers, last to first (:153-157)
     dPRE, dMOD = new(M, 128), new(M, 128)
     for i in range(5, -1, -1):
-        h_i = H5 if i == 5 else (PH[:, 63:191] if i == 4 else H[i])
-        ops.film_relu_bwd(dH, PRE[i], MOD, h_i, dPRE, dMOD, i != 5)
+        ops.film_relu_bwd(dH, PRE[i], MOD, dPRE, dMOD, i != 5, G[f"pts_linears.{i}.bias"])     # bias grad = colsum(dPRE)
         x_i = PH[:, :63] if i == 0 else (PH[:, :191] if i == 5 else H[i - 1])
-        ops.linear_bwd_weight(dPRE, x_i, G[f"pts_linears.{i}.weight"], G[f"pts_linears.{i}.bias"])
+        ops.linear_bwd_weight(dPRE, x_i, G[f"pts_linears.{i}.weight"], None)
         if i == 0:
             break
         W = P[f"pts_linears.{i}.weight"]
