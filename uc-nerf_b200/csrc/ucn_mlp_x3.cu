@@ -416,28 +416,34 @@ mlp_x3_kernel(const __grid_constant__ Plan plan, const unsigned char *__restrict
           head[0] = head[1] = head[2] = head[3] = 0.f;
           epi64<0, true>(t_acc, t_mod, col0, bias_s + 128 * 5, nullptr, h_row, f32s + ucn::X3Layout::w_base, head);
           tr.ev(6, 1, g);
-          if (hf == 1) {
-            exch_s[s * 128 + row] = make_float4(head[0], head[1], head[2], head[3]);
-            named_bar_arrive(bar_id, 256);
-            // [img feats | 1] as split bf16 pairs -> TMEM acc columns 64.. (hi) and 96.. (lo): A operand of fb
+          // [img feats | 1] as split bf16 pairs -> TMEM acc columns 64.. (hi) and 96.. (lo): A operand of fb.  The two
+          // warpgroups of the slot stage half of the words each (words 8*half .. 8*half+7 of every 16-word pass), once
+          // warpgroup 1 has finished reading those accumulator columns (the named barrier below).
+          auto stage_fb_half = [&](int half) {
 #pragma unroll 1
             for (int h16 = 0; h16 < (L.Kfb + 31) / 32; ++h16) {     // 32 K values (16 hi + 16 lo words) per pass
-              uint32_t hi[16], lo[16];
+              uint32_t hi[8], lo[8];
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const int k = 32 * h16 + 2 * j;
+              for (int j = 0; j < 8; ++j) {
+                const int k = 32 * h16 + 16 * half + 2 * j;
                 float a = 0.f, b = 0.f;
                 if (k < Kfb_real) a = valid ? __ldg(frow + (Kfilm_real + k) * f_k_stride) : 0.f; else if (k == Kfb_real) a = 1.f;
                 if (k + 1 < Kfb_real) b = valid ? __ldg(frow + (Kfilm_real + k + 1) * f_k_stride) : 0.f; else if (k + 1 == Kfb_real) b = 1.f;
                 split2(a, b, hi[j], lo[j]);
               }
               tr.ev(6, 2, g);
-              tmem_st16(t_acc + 64 + 16 * h16, hi);
-              tmem_st16(t_acc + 96 + 16 * h16, lo);
+              tmem_st8(t_acc + 64 + 16 * h16 + 8 * half, hi);
+              tmem_st8(t_acc + 96 + 16 * h16 + 8 * half, lo);
             }
             tmem_wait_st();
+          };
+          if (hf == 1) {
+            exch_s[s * 128 + row] = make_float4(head[0], head[1], head[2], head[3]);
+            named_bar_arrive(bar_id, 256);
+            stage_fb_half(0);
           } else {
             named_bar_sync(bar_id, 256);
+            stage_fb_half(1);
             const float4 o = exch_s[s * 128 + row];
             const float *bb = f32s + ucn::X3Layout::b_base;
             base4[0] = head[0] + o.x + bb[0]; base4[1] = head[1] + o.y + bb[1];
