@@ -7,8 +7,9 @@ confidence require grad), batch_size 1024 (50 confidence-drawn 4x4 patches + 224
 rays = 2 048 rays:
 
     build_rays (selection in PyTorch, sampling on K1)  ->  rendering (K2, K3 training primitives, K4)
-    ->  loss = 5 * img2mse + 0.05 * weighted sparse-depth MSE      (train.py:171-188; the patch smoothness /
-        scale-invariant terms and cas_mvsnet_loss act on encoder outputs and are 8(f) "next" rows)
+    ->  loss = 5 * img2mse + 0.05 * (weighted sparse-depth MSE + edge-preserving patch smoothness)
+               + 0.008 * scale-invariant patch gradient loss      (train.py:164-188, ucnerf_b200/losses.py;
+        cas_mvsnet_loss acts on the encoder's outputs and is not part of this path)
     ->  backward (K4b, K3b, K2b)  ->  one all-reduce(sum)/P of the flat gradient bucket  ->  Adam step
 
 Every rank has its own target pose and sampling seed (data parallel); the only collective is the gradient bucket
@@ -92,7 +93,7 @@ def run(args, ClockSampler, peaks):
     import torch
     import torch.distributed as dist
     from types import SimpleNamespace
-    from ucnerf_b200 import lib as L, models, rays, renderer, synthetic, train_path as TP
+    from ucnerf_b200 import lib as L, losses, models, rays, renderer, synthetic, train_path as TP
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -128,6 +129,7 @@ def run(args, ClockSampler, peaks):
     imgs_full = torch.cat([target_img, src_imgs.reshape(1, V, 3, H, W)], dim=1)
     sparse_depths = (sc.near_fars[0, 0] + (sc.near_fars[0, 1] - sc.near_fars[0, 0]) * torch.rand((1, H, W), generator=gen)).to(dev)
     sparse_weights = torch.ones((1, H, W), device=dev)
+    dpt = (1.0 + torch.rand((1, H, W), generator=gen)).to(dev)              # monocular depth prior (train.py:174)
     w2cs, c2ws, Ks, near_fars = T(sc.w2cs), T(sc.c2ws), T(sc.K), T(sc.near_fars)
     targs = SimpleNamespace(view_num=V + 1, feat_dim=sc.feat_dim, img_downscale=1.0, use_color_volume=False,
                             net_type="v0", netchunk=1 << 20, patch_num=CFG["patch_num"], patch_size=CFG["patch_size"],
@@ -165,11 +167,8 @@ def run(args, ClockSampler, peaks):
         rgb, depth_pred = renderer.rendering(targs, pose_ref, pts, ndc, z, dirs, outputs, src_imgs,
                                              near_fars=near_fars[0], img_feat=outputs["stage3"]["img_feats"],
                                              confidence=conf, ndc_parameters=ndcp, network_fn=model, network_query_fn=query)
-        target_depths = sparse_depths[:, pix[0, N_rays:], pix[1, N_rays:]]
-        target_weights = sparse_weights[:, pix[0, N_rays:], pix[1, N_rays:]]
-        loss_nerf_depth = torch.mean(((depth_pred[N_rays:] - target_depths) ** 2) * target_weights)   # train.py:183-184
-        img_loss = torch.mean((rgb - target_s) ** 2)                                                   # img2mse, :187
-        loss = loss_nerf_depth * 0.05 + img_loss * 5.0
+        loss, _ = losses.render_losses(rgb, depth_pred, target_s, pix, N_rays, CFG["patch_num"], CFG["patch_size"],
+                                       sparse_depths, sparse_weights, dpt)              # train.py:164-188
         mark(2)
         opt.zero_grad(set_to_none=True)
         for t in map_leaves:
@@ -231,7 +230,7 @@ def run(args, ClockSampler, peaks):
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": NAME, **CFG, "rays_per_step_per_gpu": R, "optimizer": "Adam",
                        "arithmetic": "fp32 operands split into three bf16 parts, six tcgen05 MMAs per product, fp32 accumulate (fp32-class: gradients within 1e-4 of the reference's autograd); heads and elementwise in fp32",
-                       "loss": "5*img2mse + 0.05*weighted sparse-depth MSE (train.py:183-188)",
+                       "loss": "5*img2mse + 0.05*(weighted sparse-depth MSE + patch smoothness) + 0.008*scale-invariant patch gradient (train.py:164-188 minus the encoder-side cas_mvsnet_loss)",
                        "l2": "saved activations 2.7 GB per step exceed the 126 MB L2",
                        "parallelism": f"data parallel x{world}: one all-reduce of {n_grad_params} fp32 gradients per step"},
             "e2e": {"value": world * R / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": n_depth * 16,

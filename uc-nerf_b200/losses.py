@@ -1,0 +1,70 @@
+"""Renderer-side loss terms of the training step (train.py:164-190) -- host-side glue in PyTorch.
+
+These are the terms of the reference's loss that act on the renderer's outputs (rgb, depth of the selected rays); they
+run on ~2 048 rays and 50 4x4 patches, so they stay elementwise torch code (SURVEY.md 8f rank 3 lists fusing them as
+a later row).  `cas_mvsnet_loss` (network/mvs_models.py:504-530) acts on the encoder's outputs and is not part of
+this path.
+
+    utils/utils.py:11-12         img2mse, mse2psnr
+    network/mvs_models.py:491-509 EdgePreservingSmoothnessLoss  -> edge_preserving_smoothness
+    utils/loss.py:54-112          compute_scale_and_shift + gradient_loss + GradientLoss -> scale_invariant_gradient
+    train.py:164-188              the weighted sum -> render_losses
+"""
+import torch
+
+
+def img2mse(x, y):
+    return torch.mean((x - y) ** 2)
+
+
+def mse2psnr(x):
+    return -10.0 * torch.log10(x)
+
+
+def edge_preserving_smoothness(depth, guide, gamma: float = 0.1):
+    """depth [P,h,w], guide [P,h,w,C]: mean |w * d depth| over the four neighbour directions, with bilateral weights
+    w = exp(-|d guide|_1 / gamma) from the guide (the monocular depth prior in train.py:174-178)."""
+    def pairs(t):
+        return ((t[:, :, :-1], t[:, :, 1:]), (t[:, :-1, :], t[:, 1:, :]), (t[:, :-1, :-1], t[:, 1:, 1:]),
+                (t[:, 1:, :-1], t[:, :-1, 1:]))
+    total = 0.0
+    for (g0, g1), (d0, d1) in zip(pairs(guide), pairs(depth)):
+        w = torch.exp(-(g0 - g1).abs().sum(-1) / gamma)
+        total = total + (w * (d0 - d1)).abs().mean()
+    return total / 4
+
+
+def scale_invariant_gradient(pred, target, mask=None):
+    """pred, target [P,h,w]: align pred to target per patch by the least-squares scale and shift, then sum the L1 norms of
+    the horizontal and vertical gradients of the residual, divided by P (utils/loss.py:54-112; the masks are only used
+    by the alignment there, as here)."""
+    mask = torch.ones_like(pred) if mask is None else mask
+    a00, a01, a11 = (mask * pred * pred).sum((1, 2)), (mask * pred).sum((1, 2)), mask.sum((1, 2))
+    b0, b1 = (mask * pred * target).sum((1, 2)), (mask * target).sum((1, 2))
+    det = a00 * a11 - a01 * a01
+    ok = det != 0
+    safe = torch.where(ok, det, torch.ones_like(det))
+    scale = torch.where(ok, (a11 * b0 - a01 * b1) / safe, torch.zeros_like(det))
+    shift = torch.where(ok, (-a01 * b0 + a00 * b1) / safe, torch.zeros_like(det))
+    diff = scale.view(-1, 1, 1) * pred + shift.view(-1, 1, 1) - target
+    gx = (diff[:, :, 1:] - diff[:, :, :-1]).abs().sum((1, 2))
+    gy = (diff[:, 1:, :] - diff[:, :-1, :]).abs().sum((1, 2))
+    return (gx + gy).sum() / pred.shape[0]
+
+
+def render_losses(rgb, depth_pred, target_s, pix, N_rays, patch_num, patch_size, sparse_depths, sparse_weights, dpt):
+    """The renderer-side part of train.py:164-188: -> (loss, dict of terms).
+    rgb [R,3], depth_pred [R], target_s [R,3], pix [2,R] int64 (rows, cols); the first patch_num*patch_size^2 rays are
+    the patches, rays N_rays.. are the sparse-depth rays; sparse_depths / sparse_weights / dpt [1,H,W]."""
+    ps, half = patch_size, patch_num // 2
+    patch_pts = patch_num * ps * ps
+    target_depths = sparse_depths[:, pix[0, N_rays:], pix[1, N_rays:]]
+    target_weights = sparse_weights[:, pix[0, N_rays:], pix[1, N_rays:]]
+    patch_depth = depth_pred[:patch_pts].reshape(-1, ps, ps)
+    patch_dpt = dpt[:, pix[0, :patch_pts], pix[1, :patch_pts]].reshape(-1, ps, ps, 1)
+    smooth = edge_preserving_smoothness(patch_depth[:half], patch_dpt[:half])
+    nerf_depth = torch.mean(((depth_pred[N_rays:] - target_depths) ** 2) * target_weights)
+    scale_inv = scale_invariant_gradient(patch_depth[half:], patch_dpt[half:].squeeze(-1))
+    img = img2mse(rgb, target_s)
+    loss = nerf_depth * 0.05 + smooth * 0.05 + scale_inv * 0.008 + img * 5.0
+    return loss, {"img": img, "nerf_depth": nerf_depth, "smooth": smooth, "scale_invariant": scale_inv}
