@@ -226,9 +226,14 @@ def main():
     from ucnerf_b200.frame import HostSweep
     sweep = HostSweep(pw, pack, n_rays, args.mode, dev, max_rays=max_rays)
 
-    def step_e2e(i, last):
-        # view i from pinned host maps -> pinned host image; view i+1's maps cross PCIe while view i renders
-        sweep.render(i, host, None if last else host, seed=i)
+    def step_e2e(i, n):
+        # view i from pinned host maps -> pinned host image; view i+1's maps cross PCIe while view i renders, and
+        # view i+1 is submitted before view i is collected, so the GPU does not idle while the host builds a frame
+        if i == 0:
+            sweep.submit(0, host, host if n > 1 else None, seed=0)
+        if i + 1 < n:
+            sweep.submit(i + 1, host, host if i + 2 < n else None, seed=i + 1)
+        return sweep.result(i)
 
     def barrier():
         if world > 1:
@@ -253,7 +258,7 @@ def main():
     for i in range(args.warmup):
         step_resident({}, 1000 + i)
     for i in range(max(2, args.warmup // 2)):
-        step_e2e(i, i + 1 == max(2, args.warmup // 2))
+        step_e2e(i, max(2, args.warmup // 2))
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -262,7 +267,7 @@ def main():
     ms, wall_ms = timed(lambda i: step_resident(timers, i), args.steps)
     launches = L.launch_count() // args.steps
     clocks = sampler.stop() if rank == 0 else None
-    e2e_ms, e2e_wall = timed(lambda i: step_e2e(i, i + 1 == args.steps), args.steps)
+    e2e_ms, e2e_wall = timed(lambda i: step_e2e(i, args.steps), args.steps)
     e2e_ms = max(e2e_ms, e2e_wall)                       # host work is part of the end-to-end call
 
     kern = {k: sum(a.elapsed_time(b) for a, b in v) / args.steps for k, v in timers.items()}   # ms per step

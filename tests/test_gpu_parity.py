@@ -346,3 +346,16 @@ def test_host_sweep_matches_frame_renderer():
         out = sweep.render(i, maps[i], maps[i + 1] if i + 1 < len(maps) else None, seed=7).clone()
         rgb, depth = FrameRenderer(PackedFrame.from_scene(sc, S, DEV, dir_switch=1024), pw, "bf16").render(seed=7)
         assert torch.equal(out[:, :3], rgb.cpu()) and torch.equal(out[:, 3], depth.cpu()), i
+    # pipelined use: view i+1 is submitted before view i is collected (two views in flight); same images
+    sweep2 = HostSweep(pw, make_frame, H * W, "bf16", DEV)
+    want = []
+    for sc in scenes:
+        rgb, depth = FrameRenderer(PackedFrame.from_scene(sc, S, DEV, dir_switch=1024), pw, "bf16").render(seed=7)
+        want.append(torch.cat((rgb, depth[:, None]), 1).cpu())
+    cur["sc"] = scenes[0]
+    sweep2.submit(0, maps[0], maps[1], seed=7)
+    for i in range(len(scenes)):
+        if i + 1 < len(scenes):
+            cur["sc"] = scenes[i + 1]
+            sweep2.submit(i + 1, maps[i + 1], maps[i + 2] if i + 2 < len(scenes) else None, seed=7)
+        assert torch.equal(sweep2.result(i), want[i]), i

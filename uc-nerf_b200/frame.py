@@ -278,7 +278,7 @@ class HostSweep:
     """Novel-view sweep from HOST maps (BASELINE config 3 shape: one set of encoder outputs per target view).
 
     ``render(i, host_maps, next_host_maps)`` renders view i from pinned host tensors and returns the image in a
-    pinned host buffer.  The maps of view i+1 are copied host->device on a side stream while view i renders
+    pinned host buffer; ``submit`` / ``result`` split the call so that a sweep can keep two views in flight.  The maps of view i+1 are copied host->device on a side stream while view i renders
     (two staging sets), so the PCIe transfer of every view is inside the sweep but off its critical path; the
     result is copied device->host and the call synchronises, as the reference's eval loop does per chunk
     (train.py:274-275).  `make_frame(dev_maps)` builds the PackedFrame (cameras + ucn_pack_* of the staged maps).
@@ -297,7 +297,10 @@ class HostSweep:
         self.renderer: Optional[FrameRenderer] = None
         self.rgb = torch.empty((self.n_rays, 3), device=self.device)
         self.depth = torch.empty((self.n_rays,), device=self.device)
-        self.out_host = torch.empty((self.n_rays, 4), dtype=torch.float32).pin_memory()
+        self.out_dev = [torch.empty((self.n_rays, 4), device=self.device) for _ in range(2)]
+        self.out_host = [torch.empty((self.n_rays, 4), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.done = [torch.cuda.Event(), torch.cuda.Event()]
+        self._frames = [None, None]
         for e in self.free:
             e.record(torch.cuda.current_stream(self.device))
 
@@ -319,7 +322,10 @@ class HostSweep:
             self.copied[slot].record(self.copy_stream)
         self.pending[slot] = tag
 
-    def render(self, i: int, host_maps, next_host_maps=None, seed: int = 0):
+    def submit(self, i: int, host_maps, next_host_maps=None, seed: int = 0):
+        """Enqueue view i (host->device copy if not prefetched, K0 packing, K1..K4, device->host copy of the image) and
+        return without synchronising; `result(i)` waits for it.  Submitting view i+1 before collecting view i keeps the
+        GPU busy while the host builds the next frame (at most two views in flight: two staging sets, two images)."""
         slot = i & 1
         main = torch.cuda.current_stream(self.device)
         if self.pending[slot] != i:
@@ -331,10 +337,20 @@ class HostSweep:
         if self.renderer is None:
             self.renderer = FrameRenderer(fr, self.weights, self.mode, max_rays=self.max_rays)
         self.renderer.frame = fr
+        self._frames[slot] = fr                                     # keeps the packed maps alive until the view is collected
         self.renderer.render(seed=seed, out_rgb=self.rgb, out_depth=self.depth)
         self.free[slot].record(main)
-        self.out_host[:, :3].copy_(self.rgb, non_blocking=True)
-        self.out_host[:, 3].copy_(self.depth, non_blocking=True)
-        main.synchronize()                                          # the caller reads the image
+        torch.cat((self.rgb, self.depth[:, None]), dim=1, out=self.out_dev[slot])
+        self.out_host[slot].copy_(self.out_dev[slot], non_blocking=True)
+        self.done[slot].record(main)
         self.pending[slot] = None
-        return self.out_host
+
+    def result(self, i: int) -> torch.Tensor:
+        """Pinned host image [n_rays, 4] = (rgb, depth) of view i (valid until view i+2 is submitted)."""
+        self.done[i & 1].synchronize()
+        return self.out_host[i & 1]
+
+    def render(self, i: int, host_maps, next_host_maps=None, seed: int = 0):
+        """submit + result: one view, synchronous (the reference's eval loop syncs per chunk, train.py:274-275)."""
+        self.submit(i, host_maps, next_host_maps, seed)
+        return self.result(i)
