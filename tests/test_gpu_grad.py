@@ -248,3 +248,65 @@ def test_training_pixel_selection_properties():
     assert torch.equal(pix[:, N:].long(), coords.t())
     with pytest.raises(Exception):
         rays.select_training_pixels(H, W, conf, coords, pn * ps * ps - 1, pn, ps)        # quirk Q20
+
+
+@pytest.mark.parametrize("R,S,V", ((37, 12, 3), (1, 3, 1), (5, 126, 5), (300, 3, 2)))
+def test_mlp_train_ragged_and_tiny_batches(R, S, V, gemm):
+    """Sample counts that are not multiples of the 128-row tensor-core tile (444), a single ray with the minimum S=3,
+    V=1 .. 5 source views: CUDA primitives vs the CPU restatement (oracle/train_ops.py) on the same random inputs."""
+    from ucnerf_b200 import synthetic, train_path as TP
+    TOL = gemm
+    rng = np.random.default_rng(R * 1000 + S * 10 + V)
+    F = 24 + 12 * V + 1
+    M = R * S
+    wts = synthetic.make_weights(V, seed=5)
+    feat = rng.standard_normal((M, F)).astype(np.float32)
+    feat[:, -1] = rng.random(M).astype(np.float32)                      # confidence in [0, 1)
+    ndc = rng.random((M, 3)).astype(np.float32)
+    ang = rng.standard_normal((R, 3)).astype(np.float32)
+    ang /= np.linalg.norm(ang, axis=1, keepdims=True)
+    d_raw = rng.standard_normal((M, 4)).astype(np.float32)
+    Tc = torch.from_numpy
+    Pc = {n: Tc(np.ascontiguousarray(wts["nerf." + n])) for n in TP.PARAM_NAMES}
+    raw_c, saved_c = TP.mlp_forward_train(OracleOps(), Pc, Tc(ndc.copy()), Tc(ang.copy()), Tc(feat.copy()), S)
+    Gc = {n: torch.zeros_like(p) for n, p in Pc.items()}
+    dfeat_c = TP.mlp_backward(OracleOps(), Pc, saved_c, Tc(d_raw.copy()), Gc)
+    Pg = {n: T(wts["nerf." + n]) for n in TP.PARAM_NAMES}
+    raw_g, saved_g = TP.mlp_forward_train(TP.CudaOps(), Pg, T(ndc), T(ang), T(feat), S)
+    Gg = {n: torch.zeros_like(p) for n, p in Pg.items()}
+    dfeat_g = TP.mlp_backward(TP.CudaOps(), Pg, saved_g, T(d_raw), Gg)
+    assert np.abs(raw_g.cpu().numpy()[:, :3] - raw_c.numpy()[:, :3]).max() <= 1e-4
+    assert rel_err(raw_g.cpu().numpy()[:, 3], raw_c.numpy()[:, 3]) <= 1e-4
+    assert rel_err(dfeat_g.cpu().numpy(), dfeat_c.numpy()) <= TOL
+    for n in TP.PARAM_NAMES:
+        assert rel_err(Gg[n].cpu().numpy(), Gc[n].numpy()) <= TOL, n
+
+
+def test_backward_edge_cases():
+    """Empty batches are no-ops; white background and out-of-frustum samples go through K4b / K2b without NaNs."""
+    from ucnerf_b200 import lib as L
+    from ucnerf_b200.frame import PackedFrame
+    from ucnerf_b200 import synthetic
+    lib = L.load()
+    one = torch.zeros((1, 12, 4), device=DEV)
+    z = torch.zeros((1, 12), device=DEV)
+    g3, g1, dr = torch.zeros((1, 3), device=DEV), torch.zeros((1,), device=DEV), torch.ones((1, 12, 4), device=DEV)
+    L.check(lib.ucn_composite_bwd(L.ptr(one), L.ptr(z), 0, 12, 0, L.ptr(g3), L.ptr(g1), L.ptr(dr), L.stream_ptr()))
+    assert float(dr.min()) == 1.0                                       # R = 0: nothing written
+    sc = synthetic.make_scene(16, 20, 3, seed=9)
+    fr = PackedFrame.from_scene(sc, 12, device=DEV)
+    n = 64
+    far = torch.full((n, 3), 1e4, device=DEV)                         # far outside every frustum / image
+    ndc = torch.full((n, 3), 7.0, device=DEV)
+    d_feat = torch.randn((n, 24 + 12 * 3 + 1), device=DEV)
+    outs = [torch.zeros(sc.volumes[k].shape, device=DEV) for k in range(3)] + \
+           [torch.zeros(sc.img_feats.shape, device=DEV), torch.zeros(sc.confidence.shape, device=DEV)]
+    L.check(lib.ucn_gather_bwd(C.byref(fr.c), L.ptr(far), L.ptr(ndc), L.ptr(ndc), L.ptr(ndc), n, L.ptr(d_feat),
+                               *[L.ptr(o) for o in outs], L.stream_ptr()))
+    L.check(lib.ucn_gather_bwd(C.byref(fr.c), L.ptr(far), L.ptr(ndc), L.ptr(ndc), L.ptr(ndc), 0, L.ptr(d_feat),
+                               *[L.ptr(o) for o in outs], L.stream_ptr()))
+    for o in outs:
+        assert bool(torch.isfinite(o).all())
+    # border padding: a clamped sample deposits its whole cotangent on border texels (weights sum to 1 per sample)
+    assert abs(float(outs[4].sum()) - float(d_feat[:, -1].sum())) <= 1e-3 * float(d_feat[:, -1].abs().sum())
+    assert abs(float(outs[0].sum()) - float(d_feat[:, :8].sum())) <= 1e-3 * float(d_feat[:, :8].abs().sum())
