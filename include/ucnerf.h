@@ -239,6 +239,16 @@ int ucn_render_rays(const ucn_frame *f, const ucn_weights *w, int ray0, int R, c
                     const float *t_rand, uint64_t seed, int mode, void *workspace, size_t workspace_bytes,
                     float *out_rgb, float *out_depth, void *stream);
 
+/* ---- multi-GPU: peer-mapped frame buffer (the reference is single-GPU, train.py:433) ------ */
+/* One process per GPU.  The root allocates the [H*W][4]-float frame buffer and exports a 64-byte CUDA IPC handle;
+ * every other process opens it with its own device current and passes tile pointers inside it as ucn_render_rays'
+ * out_rgb / out_depth, so K4's stores land in the root's HBM over NVLink (no gather collective). */
+#define UCN_PEER_HANDLE_BYTES 64
+int ucn_peer_alloc(size_t bytes, void **dptr, unsigned char *handle);
+int ucn_peer_open(const unsigned char *handle, void **dptr);
+int ucn_peer_close(void *dptr);
+int ucn_peer_free(void *dptr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,6 +37,29 @@ ms = torch.tensor([e0.elapsed_time(e1) / 10], device=dev)
 dist.all_reduce(ms, op=dist.ReduceOp.MAX)
 ok = torch.tensor([int(same)], device=dev)
 dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+
+# the same frame with K4 storing every rank's tile straight into rank 0's frame buffer over NVLink (no all-gather)
+buf = shard.PeerFrameBuffer(H, W, dev, root=0)
+
+def render_into(ray0, n, out_rgb, out_depth):
+    ren.render(ray0, n, t_rand=t_rand[ray0:ray0 + n], out_rgb=out_rgb, out_depth=out_depth)
+
+res = shard.render_sharded_p2p(render_into, buf, row_align=8)
+p2p_same = True if res is None else bool(torch.equal(res[0], full_rgb) and torch.equal(res[1], full_depth))
+for _ in range(3):
+    shard.render_sharded_p2p(render_into, buf, row_align=8)
+dist.barrier(); torch.cuda.synchronize()
+t0 = time.perf_counter()
+for _ in range(10):
+    shard.render_sharded_p2p(render_into, buf, row_align=8)
+p2p_ms = torch.tensor([(time.perf_counter() - t0) * 100.0], device=dev)       # wall ms per frame (ends with a barrier)
+dist.all_reduce(p2p_ms, op=dist.ReduceOp.MAX)
+t0 = time.perf_counter()
+for _ in range(10):
+    shard.render_sharded(render_rays, H, W, row_align=8)
+    torch.cuda.synchronize()
+ag_ms = torch.tensor([(time.perf_counter() - t0) * 100.0], device=dev)
+dist.all_reduce(ag_ms, op=dist.ReduceOp.MAX)
 if rank == 0:
     from oracle import oracle as O
     O.set_num_threads(os.cpu_count())
@@ -47,6 +70,10 @@ if rank == 0:
     print(json.dumps({"check": "sharded render == single-GPU render (bit-identical on every rank)", "n_gpus": world,
                       "bit_identical": bool(ok.item()), "max_abs_rgb_err_vs_oracle": err, "gate": 1e-3,
                       "frame": f"{W}x{H}, S={S}, V'={V}", "sharded_frame_ms": ms.item(),
-                      "rays_per_s": H * W / (ms.item() * 1e-3)}))
-    assert ok.item() == 1 and err <= 1e-3
+                      "rays_per_s": H * W / (ms.item() * 1e-3),
+                      "p2p_epilogue": {"what": "K4 stores each tile into rank 0's frame buffer over NVLink (CUDA IPC), one barrier",
+                                       "bit_identical_on_root": p2p_same, "wall_ms_per_frame": p2p_ms.item(),
+                                       "allgather_wall_ms_per_frame": ag_ms.item()}}))
+    assert ok.item() == 1 and err <= 1e-3 and p2p_same
+buf.close()
 dist.destroy_process_group()

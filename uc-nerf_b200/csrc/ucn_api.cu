@@ -48,6 +48,40 @@ extern "C" int ucn_check_device(void) {
   return UCN_OK;
 }
 
+// ---- peer-mapped buffers (one process per GPU; CUDA IPC over NVLink) ---------------------------------------------
+// The owner allocates with cudaMalloc (its own allocation, so the IPC handle maps exactly this buffer) and exports
+// a handle; every other process opens it WITH ITS OWN DEVICE CURRENT, which is what makes the mapping addressable
+// by that device's kernels (cudaIpcMemLazyEnablePeerAccess) -- K4 then stores its tile straight into the owner's HBM.
+static_assert(sizeof(cudaIpcMemHandle_t) == UCN_PEER_HANDLE_BYTES, "IPC handle size");
+extern "C" int ucn_peer_alloc(size_t bytes, void **dptr, unsigned char *handle) {
+  UCN_CHECK_ARG(dptr && handle && bytes > 0, "ucn_peer_alloc: null argument / zero size");
+  cudaError_t e = cudaMalloc(dptr, bytes);
+  if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_peer_alloc: cudaMalloc");
+  cudaIpcMemHandle_t h;
+  e = cudaIpcGetMemHandle(&h, *dptr);
+  if (e != cudaSuccess) { cudaFree(*dptr); *dptr = nullptr; return ucn_cuda_status(e, "ucn_peer_alloc: cudaIpcGetMemHandle"); }
+  memcpy(handle, &h, sizeof(h));
+  return UCN_OK;
+}
+extern "C" int ucn_peer_open(const unsigned char *handle, void **dptr) {
+  UCN_CHECK_ARG(dptr && handle, "ucn_peer_open: null argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  cudaError_t e = cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_peer_open: cudaIpcOpenMemHandle");
+  return UCN_OK;
+}
+extern "C" int ucn_peer_close(void *dptr) {
+  if (!dptr) return UCN_OK;
+  cudaError_t e = cudaIpcCloseMemHandle(dptr);
+  return e == cudaSuccess ? UCN_OK : ucn_cuda_status(e, "ucn_peer_close");
+}
+extern "C" int ucn_peer_free(void *dptr) {
+  if (!dptr) return UCN_OK;
+  cudaError_t e = cudaFree(dptr);
+  return e == cudaSuccess ? UCN_OK : ucn_cuda_status(e, "ucn_peer_free");
+}
+
 extern "C" int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const float *feat, const float *angle,
                                int R, int S, float *raw, int mode, void *stream) {
   UCN_CHECK_ARG(w && ndc_pts && feat && angle && raw, "ucn_mlp_forward: null argument");
