@@ -324,7 +324,18 @@ skinny_bwd_weight_kernel(const float *__restrict__ dY, long long ldy, const floa
   if (k >= K) return;
   const long long m0 = (long long)blockIdx.x * m_chunk, m1 = min(M, m0 + m_chunk);
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (long long m = m0; m < m1; ++m) {
+  long long m = m0;
+  for (; m + 8 <= m1; m += 8) {                                   // eight independent row loads in flight per thread
+    float x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = X[(m + i) * ldx + k];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int n = 0; n < 4; ++n)
+        if (n < N) acc[n] = fmaf(dY[(m + i) * ldy + n], x[i], acc[n]);
+  }
+  for (; m < m1; ++m) {
     const float x = X[m * ldx + k];
 #pragma unroll
     for (int n = 0; n < 4; ++n)
@@ -456,6 +467,144 @@ __global__ void blend_bwd_kernel(const float4 *__restrict__ d_raw, const float4 
   d_conf[m * lddconf] = -du;                 // u = 1 - confidence
 }
 
+// ---- 16-byte variants of the streaming kernels above ------------------------------------------------------------------
+// One float4 per thread and per operand (4x the bytes in flight of the scalar kernels, which reach 35-60 % of the HBM
+// roofline at M = 258 048); the launchers use them whenever every pointer is 16-byte aligned and every pitch a multiple
+// of four floats, and fall back to the scalar kernels otherwise (h of pts layer 4 lives at column 63 of [PE63 | h]:
+// its loads / stores stay scalar through the ALIGNED template flag).
+template <bool ALIGNED> __device__ __forceinline__ float4 ld4(const float *p) {
+  if (ALIGNED) return *reinterpret_cast<const float4 *>(p);
+  return make_float4(p[0], p[1], p[2], p[3]);
+}
+template <bool ALIGNED> __device__ __forceinline__ void st4(float *p, const float4 v) {
+  if (ALIGNED) { *reinterpret_cast<float4 *>(p) = v; return; }
+  p[0] = v.x; p[1] = v.y; p[2] = v.z; p[3] = v.w;
+}
+inline bool al16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <bool H_AL>
+__global__ void __launch_bounds__(256)
+film_relu_fwd_v4_kernel(const float *__restrict__ pre, const float *__restrict__ mod, float *__restrict__ h, long long ldh,
+                        long long M) {
+  const long long e4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e4 >= M * 32) return;
+  const float4 p = ld4<true>(pre + 4 * e4), md = ld4<true>(mod + 4 * e4);
+  st4<H_AL>(h + (e4 >> 5) * ldh + 4 * (e4 & 31),
+            make_float4(fmaxf(p.x * md.x, 0.0f), fmaxf(p.y * md.y, 0.0f), fmaxf(p.z * md.z, 0.0f), fmaxf(p.w * md.w, 0.0f)));
+}
+// 128 threads = 4 rows x 32 column groups per pass, 64 rows per block; column sums through shared memory
+template <bool DH_AL>
+__global__ void __launch_bounds__(128)
+film_relu_bwd_v4_kernel(const float *__restrict__ dh, long long lddh, const float *__restrict__ pre,
+                        const float *__restrict__ mod, float *__restrict__ dpre, float *__restrict__ dmod, int accumulate,
+                        float *db, long long M) {
+  const int cg = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  const long long m0 = (long long)blockIdx.x * 64;
+  float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+  for (int i = 0; i < 16; ++i) {
+    const long long m = m0 + 4 * i + rg;
+    if (m >= M) break;
+    const long long e = m * 128 + 4 * cg;
+    const float4 p = ld4<true>(pre + e), md = ld4<true>(mod + e), g0 = ld4<DH_AL>(dh + m * lddh + 4 * cg);
+    float4 dm = accumulate ? ld4<true>(dmod + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 g = make_float4(p.x * md.x > 0.0f ? g0.x : 0.0f, p.y * md.y > 0.0f ? g0.y : 0.0f,
+                                 p.z * md.z > 0.0f ? g0.z : 0.0f, p.w * md.w > 0.0f ? g0.w : 0.0f);
+    const float4 dp = make_float4(g.x * md.x, g.y * md.y, g.z * md.z, g.w * md.w);
+    st4<true>(dpre + e, dp);
+    sum.x += dp.x; sum.y += dp.y; sum.z += dp.z; sum.w += dp.w;
+    dm.x += g.x * p.x; dm.y += g.y * p.y; dm.z += g.z * p.z; dm.w += g.w * p.w;
+    st4<true>(dmod + e, dm);
+  }
+  if (db) {
+    __shared__ float4 part[4][32];
+    part[rg][cg] = sum;
+    __syncthreads();
+    if (rg == 0) {
+#pragma unroll
+      for (int k = 1; k < 4; ++k) { const float4 o = part[k][cg]; sum.x += o.x; sum.y += o.y; sum.z += o.z; sum.w += o.w; }
+      atomicAdd(db + 4 * cg, sum.x); atomicAdd(db + 4 * cg + 1, sum.y);
+      atomicAdd(db + 4 * cg + 2, sum.z); atomicAdd(db + 4 * cg + 3, sum.w);
+    }
+  }
+}
+template <bool A_AL>
+__global__ void __launch_bounds__(256)
+mul_fwd_v4_kernel(const float *__restrict__ a, long long lda, const float *__restrict__ b, float *__restrict__ o, long long M) {
+  const long long e4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e4 >= M * 32) return;
+  const float4 x = ld4<A_AL>(a + (e4 >> 5) * lda + 4 * (e4 & 31)), y = ld4<true>(b + 4 * e4);
+  st4<true>(o + 4 * e4, make_float4(x.x * y.x, x.y * y.y, x.z * y.z, x.w * y.w));
+}
+template <bool A_AL>
+__global__ void __launch_bounds__(256)
+mul_bwd_v4_kernel(const float *__restrict__ d_o, const float *__restrict__ a, long long lda, const float *__restrict__ b,
+                  float *__restrict__ da, int accumulate, float *__restrict__ db, long long M) {
+  const long long e4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e4 >= M * 32) return;
+  const float4 g = ld4<true>(d_o + 4 * e4), y = ld4<true>(b + 4 * e4), x = ld4<A_AL>(a + (e4 >> 5) * lda + 4 * (e4 & 31));
+  float4 v = accumulate ? ld4<true>(da + 4 * e4) : make_float4(0.f, 0.f, 0.f, 0.f);
+  v.x += g.x * y.x; v.y += g.y * y.y; v.z += g.z * y.z; v.w += g.w * y.w;
+  st4<true>(da + 4 * e4, v);
+  st4<true>(db + 4 * e4, make_float4(g.x * x.x, g.y * x.y, g.z * x.z, g.w * x.w));
+}
+__global__ void __launch_bounds__(256)
+relu_bwd_v4_kernel(const float *__restrict__ dy, const float *__restrict__ y, float *__restrict__ dx, long long n4) {
+  const long long e4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e4 >= n4) return;
+  const float4 g = ld4<true>(dy + 4 * e4), v = ld4<true>(y + 4 * e4);
+  st4<true>(dx + 4 * e4, make_float4(v.x > 0.0f ? g.x : 0.0f, v.y > 0.0f ? g.y : 0.0f, v.z > 0.0f ? g.z : 0.0f, v.w > 0.0f ? g.w : 0.0f));
+}
+// heads, K a multiple of 128: forward = warp per row, one float4 per lane and 128 columns
+__global__ void __launch_bounds__(256)
+skinny_fwd_v4_kernel(const float *__restrict__ X, long long ldx, const float *__restrict__ W, long long ldw,
+                     const float *__restrict__ b, long long M, int K, int N, float *__restrict__ Y, long long ldy, int flags) {
+  const int lane = threadIdx.x & 31;
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (m >= M) return;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int k = 4 * lane; k < K; k += 128) {
+    const float4 x = ld4<true>(X + m * ldx + k);
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+      if (n < N) {
+        const float4 w = ld4<true>(W + n * ldw + k);
+        acc[n] = fmaf(x.x, w.x, fmaf(x.y, w.y, fmaf(x.z, w.z, fmaf(x.w, w.w, acc[n]))));
+      }
+  }
+#pragma unroll
+  for (int n = 0; n < 4; ++n)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], o);
+  if (lane < N) {
+    float v = lane == 0 ? acc[0] : (lane == 1 ? acc[1] : (lane == 2 ? acc[2] : acc[3]));
+    if (b) v += b[lane];
+    float *dst = Y + m * ldy + lane;
+    if (flags & G_ACCUM) v += *dst;
+    if (flags & G_RELU) v = fmaxf(v, 0.0f);
+    *dst = v;
+  }
+}
+// grad-input of the heads: thread = four consecutive k of one row
+__global__ void __launch_bounds__(256)
+skinny_bwd_input_v4_kernel(const float *__restrict__ dY, long long ldy, const float *__restrict__ W, long long ldw,
+                           long long M, int K, int N, float *__restrict__ dX, long long ldx, int flags) {
+  const long long e4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int K4 = K >> 2;
+  if (e4 >= M * K4) return;
+  const long long m = e4 / K4;
+  const int k = 4 * (int)(e4 - m * K4);
+  float *dst = dX + m * ldx + k;
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int n = 0; n < N; ++n) {
+    const float g = dY[m * ldy + n];
+    const float4 w = ld4<true>(W + n * ldw + k);
+    v.x = fmaf(g, w.x, v.x); v.y = fmaf(g, w.y, v.y); v.z = fmaf(g, w.z, v.z); v.w = fmaf(g, w.w, v.w);
+  }
+  if (flags & G_ACCUM) { const float4 o = ld4<true>(dst); v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+  st4<true>(dst, v);
+}
+
 inline unsigned nblk(long long n, int t) { return (unsigned)((n + t - 1) / t); }
 
 int launch_gemm(const float *A, long long sai, long long sap, const float *B, long long sbp, long long sbj, float *C,
@@ -508,7 +657,10 @@ extern "C" int ucn_linear_fwd(const float *X, int64_t ldx, const float *W, int64
   UCN_CHECK_ARG(X && W && Y, "ucn_linear_fwd: null argument");
   UCN_CHECK_ARG((flags & ~3) == 0, "ucn_linear_fwd: flags");
   if (N <= 4 && M > 0) {
-    skinny_fwd_kernel<<<nblk(M, 8), 256, 0, (cudaStream_t)stream>>>(X, ldx, W, ldw, b, M, K, N, Y, ldy, flags);
+    if (K % 128 == 0 && al16(X) && al16(W) && ldx % 4 == 0 && ldw % 4 == 0)
+      skinny_fwd_v4_kernel<<<nblk(M, 8), 256, 0, (cudaStream_t)stream>>>(X, ldx, W, ldw, b, M, K, N, Y, ldy, flags);
+    else
+      skinny_fwd_kernel<<<nblk(M, 8), 256, 0, (cudaStream_t)stream>>>(X, ldx, W, ldw, b, M, K, N, Y, ldy, flags);
     UCN_LAUNCH_CHECK("skinny_fwd_kernel");
     return UCN_OK;
   }
@@ -520,7 +672,10 @@ extern "C" int ucn_linear_bwd_input(const float *dY, int64_t ldy, const float *W
   UCN_CHECK_ARG(dY && W && dX, "ucn_linear_bwd_input: null argument");
   UCN_CHECK_ARG((flags & ~1) == 0, "ucn_linear_bwd_input: flags");
   if (N <= 4 && M > 0) {
-    skinny_bwd_input_kernel<<<nblk(M * K, 256), 256, 0, (cudaStream_t)stream>>>(dY, ldy, W, ldw, M, K, N, dX, ldx, flags);
+    if (K % 4 == 0 && al16(W) && al16(dX) && ldw % 4 == 0 && ldx % 4 == 0)
+      skinny_bwd_input_v4_kernel<<<nblk(M * (K / 4), 256), 256, 0, (cudaStream_t)stream>>>(dY, ldy, W, ldw, M, K, N, dX, ldx, flags);
+    else
+      skinny_bwd_input_kernel<<<nblk(M * K, 256), 256, 0, (cudaStream_t)stream>>>(dY, ldy, W, ldw, M, K, N, dX, ldx, flags);
     UCN_LAUNCH_CHECK("skinny_bwd_input_kernel");
     return UCN_OK;
   }
@@ -567,7 +722,14 @@ extern "C" int ucn_train_prep(const float *ndc, const float *angle, int S, int64
 extern "C" int ucn_film_relu_fwd(const float *pre, const float *mod, float *h, int64_t ldh, int64_t M, void *stream) {
   UCN_CHECK_ARG(pre && mod && h, "ucn_film_relu_fwd: null argument");
   if (M <= 0) return UCN_OK;
-  film_relu_fwd_kernel<<<nblk(M * 128, 256), 256, 0, (cudaStream_t)stream>>>(pre, mod, h, ldh, M);
+  if (al16(pre) && al16(mod)) {
+    if (al16(h) && ldh % 4 == 0)
+      film_relu_fwd_v4_kernel<true><<<nblk(M * 32, 256), 256, 0, (cudaStream_t)stream>>>(pre, mod, h, ldh, M);
+    else
+      film_relu_fwd_v4_kernel<false><<<nblk(M * 32, 256), 256, 0, (cudaStream_t)stream>>>(pre, mod, h, ldh, M);
+  } else {
+    film_relu_fwd_kernel<<<nblk(M * 128, 256), 256, 0, (cudaStream_t)stream>>>(pre, mod, h, ldh, M);
+  }
   UCN_LAUNCH_CHECK("film_relu_fwd_kernel");
   return UCN_OK;
 }
@@ -575,7 +737,14 @@ extern "C" int ucn_film_relu_bwd(const float *dh, int64_t lddh, const float *pre
                                  float *dmod, int accumulate, float *db, int64_t M, void *stream) {
   UCN_CHECK_ARG(dh && pre && mod && dpre && dmod, "ucn_film_relu_bwd: null argument");
   if (M <= 0) return UCN_OK;
-  film_relu_bwd_kernel<<<nblk(M, 64), 128, 0, (cudaStream_t)stream>>>(dh, lddh, pre, mod, dpre, dmod, accumulate, db, M);
+  if (al16(pre) && al16(mod) && al16(dpre) && al16(dmod) && (!db || al16(db))) {
+    if (al16(dh) && lddh % 4 == 0)
+      film_relu_bwd_v4_kernel<true><<<nblk(M, 64), 128, 0, (cudaStream_t)stream>>>(dh, lddh, pre, mod, dpre, dmod, accumulate, db, M);
+    else
+      film_relu_bwd_v4_kernel<false><<<nblk(M, 64), 128, 0, (cudaStream_t)stream>>>(dh, lddh, pre, mod, dpre, dmod, accumulate, db, M);
+  } else {
+    film_relu_bwd_kernel<<<nblk(M, 64), 128, 0, (cudaStream_t)stream>>>(dh, lddh, pre, mod, dpre, dmod, accumulate, db, M);
+  }
   UCN_LAUNCH_CHECK("film_relu_bwd_kernel");
   return UCN_OK;
 }
@@ -583,7 +752,12 @@ extern "C" int ucn_film_relu_bwd(const float *dh, int64_t lddh, const float *pre
 extern "C" int ucn_mul_fwd(const float *a, int64_t lda, const float *b, float *o, int64_t M, void *stream) {
   UCN_CHECK_ARG(a && b && o, "ucn_mul_fwd: null argument");
   if (M <= 0) return UCN_OK;
-  mul_fwd_kernel<<<nblk(M * 128, 256), 256, 0, (cudaStream_t)stream>>>(a, lda, b, o, M);
+  if (al16(b) && al16(o)) {
+    if (al16(a) && lda % 4 == 0) mul_fwd_v4_kernel<true><<<nblk(M * 32, 256), 256, 0, (cudaStream_t)stream>>>(a, lda, b, o, M);
+    else mul_fwd_v4_kernel<false><<<nblk(M * 32, 256), 256, 0, (cudaStream_t)stream>>>(a, lda, b, o, M);
+  } else {
+    mul_fwd_kernel<<<nblk(M * 128, 256), 256, 0, (cudaStream_t)stream>>>(a, lda, b, o, M);
+  }
   UCN_LAUNCH_CHECK("mul_fwd_kernel");
   return UCN_OK;
 }
@@ -591,14 +765,24 @@ extern "C" int ucn_mul_bwd(const float *d_o, const float *a, int64_t lda, const 
                            float *db, int64_t M, void *stream) {
   UCN_CHECK_ARG(d_o && a && b && da && db, "ucn_mul_bwd: null argument");
   if (M <= 0) return UCN_OK;
-  mul_bwd_kernel<<<nblk(M * 128, 256), 256, 0, (cudaStream_t)stream>>>(d_o, a, lda, b, da, accumulate, db, M);
+  if (al16(d_o) && al16(b) && al16(da) && al16(db)) {
+    if (al16(a) && lda % 4 == 0)
+      mul_bwd_v4_kernel<true><<<nblk(M * 32, 256), 256, 0, (cudaStream_t)stream>>>(d_o, a, lda, b, da, accumulate, db, M);
+    else
+      mul_bwd_v4_kernel<false><<<nblk(M * 32, 256), 256, 0, (cudaStream_t)stream>>>(d_o, a, lda, b, da, accumulate, db, M);
+  } else {
+    mul_bwd_kernel<<<nblk(M * 128, 256), 256, 0, (cudaStream_t)stream>>>(d_o, a, lda, b, da, accumulate, db, M);
+  }
   UCN_LAUNCH_CHECK("mul_bwd_kernel");
   return UCN_OK;
 }
 extern "C" int ucn_relu_bwd(const float *dy, const float *y, float *dx, int64_t n, void *stream) {
   UCN_CHECK_ARG(dy && y && dx, "ucn_relu_bwd: null argument");
   if (n <= 0) return UCN_OK;
-  relu_bwd_kernel<<<nblk(n, 256), 256, 0, (cudaStream_t)stream>>>(dy, y, dx, n);
+  if (n % 4 == 0 && al16(dy) && al16(y) && al16(dx))
+    relu_bwd_v4_kernel<<<nblk(n / 4, 256), 256, 0, (cudaStream_t)stream>>>(dy, y, dx, n / 4);
+  else
+    relu_bwd_kernel<<<nblk(n, 256), 256, 0, (cudaStream_t)stream>>>(dy, y, dx, n);
   UCN_LAUNCH_CHECK("relu_bwd_kernel");
   return UCN_OK;
 }
