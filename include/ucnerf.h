@@ -239,6 +239,22 @@ int ucn_render_rays(const ucn_frame *f, const ucn_weights *w, int ray0, int R, c
                     const float *t_rand, uint64_t seed, int mode, void *workspace, size_t workspace_bytes,
                     float *out_rgb, float *out_depth, void *stream);
 
+/* ---- evaluation metrics of a rendered frame, device-resident ---------------------- */
+/* replaces the host-side numpy evaluation of utils/utils.py:18-22 (get_psnr) and utils/evaluation.py:8-74
+ * (compute_errors, depth_evaluation).  Accumulators are fp64 and live in device memory; the caller zeroes them. */
+size_t ucn_metrics_workspace_bytes(void);
+/* *out_sum += sum (a[i]-b[i])^2;  PSNR = -10 log10(sum / n) */
+int ucn_sq_err_sum(const float *a, const float *b, int64_t n, double *out_sum, void *stream);
+/* exact medians of valid gt / pred depths (valid: min_depth < gt < max_depth and mask != 0, mask may be NULL):
+ * out_mid4 = {gt, gt, pred, pred} values of ranks (c-1)/2 and c/2 (numpy's median is their mean), *out_count = c */
+int ucn_depth_median(const float *gt, const float *pred, const unsigned char *mask, int64_t n, float min_depth,
+                     float max_depth, void *workspace, size_t workspace_bytes, float *out_mid4, int64_t *out_count,
+                     void *stream);
+/* out8 += {sum |gt-p|/gt, sum (gt-p)^2/gt, sum (gt-p)^2, sum (log gt - log p)^2, #[t<1.25], #[t<1.25^2],
+ * #[t<1.25^3], #valid},  p = clamp(pred*ratio, min_depth, max_depth),  t = max(gt/p, p/gt) */
+int ucn_depth_errors(const float *gt, const float *pred, const unsigned char *mask, int64_t n, float min_depth,
+                     float max_depth, float ratio, double *out8, void *stream);
+
 /* ---- multi-GPU: peer-mapped frame buffer (the reference is single-GPU, train.py:433) ------ */
 /* One process per GPU.  The root allocates the [H*W][4]-float frame buffer and exports a 64-byte CUDA IPC handle;
  * every other process opens it with its own device current and passes tile pointers inside it as ucn_render_rays'
