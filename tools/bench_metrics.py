@@ -53,4 +53,4 @@ print(json.dumps({"what": "depth_evaluation + get_psnr of 4 frames 640x512 (conf
                   "max_rel_diff_depth": float(np.max(np.abs(d_gpu - d_cpu) / np.maximum(np.abs(d_cpu), 1e-30))),
                   "max_abs_diff_psnr": float(np.max(np.abs(p_gpu - p_cpu))),
                   "depth_err_kernel": {"ms": err_ms, "algorithmic_bytes": 8 * n, "GBps": 8 * n / err_ms / 1e6,
-                                       "note": "5.2 MB per launch: smaller than L2 and launch-latency sized; the figure is a lower bound of what the kernel does on resident frames"}}))
+                                       "note": "10.5 MB per launch: smaller than L2 and launch-latency sized; the figure is a lower bound of what the kernel does on resident frames"}}))
