@@ -239,6 +239,15 @@ int ucn_render_rays(const ucn_frame *f, const ucn_weights *w, int ray0, int R, c
                     const float *t_rand, uint64_t seed, int mode, void *workspace, size_t workspace_bytes,
                     float *out_rgb, float *out_depth, void *stream);
 
+/* ---- the step before the path: homography warp + variance cost volume -------------- */
+/* replaces utils/utils.py:1105-1172 (homo_warp) and the per-view loop of network/mvs_models.py:603-628.
+ * B = 1.  depth_values [D][H+2pad][W+2pad] (already replicate-padded), matrices (src_proj @ ref_proj_inv)[:3]
+ * row-major in HOST memory.  warped [C][D][Hp][Wp]; grids [D][Hp*Wp][2] normalised coordinates. */
+int ucn_homo_warp(const float *src_feat, int C, int H, int W, const float *proj12_host, const float *depth_values,
+                  const float *grid_in, int D, int pad, float *warped, float *grid_out, void *stream);
+int ucn_cost_volume_variance(const float *feats, int V, int C, int H, int W, const float *projs_host,
+                             const float *depth_values, int D, int pad, int extra_ones, float *var, void *stream);
+
 /* ---- evaluation metrics of a rendered frame, device-resident ---------------------- */
 /* replaces the host-side numpy evaluation of utils/utils.py:18-22 (get_psnr) and utils/evaluation.py:8-74
  * (compute_errors, depth_evaluation).  Accumulators are fp64 and live in device memory; the caller zeroes them. */
