@@ -167,8 +167,9 @@ def run(args, ClockSampler, peaks):
         rgb, depth_pred = renderer.rendering(targs, pose_ref, pts, ndc, z, dirs, outputs, src_imgs,
                                              near_fars=near_fars[0], img_feat=outputs["stage3"]["img_feats"],
                                              confidence=conf, ndc_parameters=ndcp, network_fn=model, network_query_fn=query)
-        loss, _ = losses.render_losses(rgb, depth_pred, target_s, pix, N_rays, CFG["patch_num"], CFG["patch_size"],
-                                       sparse_depths, sparse_weights, dpt)              # train.py:164-188
+        # train.py:164-188: value and gradient of every renderer-side term from one launch (ucn_render_losses)
+        loss, _ = losses.render_losses_fused(rgb, depth_pred, target_s, pix, N_rays, CFG["patch_num"], CFG["patch_size"],
+                                             sparse_depths, sparse_weights, dpt)
         mark(2)
         opt.zero_grad(set_to_none=True)
         for t in map_leaves:

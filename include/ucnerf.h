@@ -239,6 +239,16 @@ int ucn_render_rays(const ucn_frame *f, const ucn_weights *w, int ray0, int R, c
                     const float *t_rand, uint64_t seed, int mode, void *workspace, size_t workspace_bytes,
                     float *out_rgb, float *out_depth, void *stream);
 
+/* ---- renderer-side training loss, value and gradient in one launch ------------------- */
+/* replaces train.py:164-188 (img2mse, weighted sparse-depth MSE, weighted sum), network/mvs_models.py:491-509
+ * (EdgePreservingSmoothnessLoss), utils/loss.py:54-112 (GradientLoss) and their autograd graph.
+ * terms5 = {loss, img, nerf_depth, smooth, scale_invariant}; d_rgb [R][3], d_depth [R] = d loss / d (rgb, depth).
+ * rays [0, patch_num*patch_size^2): patches (first half smoothness, second half scale-invariant); [N_rays, R): sparse depth */
+int ucn_render_losses(const float *rgb, const float *depth, const float *target_rgb, const int64_t *pix_rows,
+                      const int64_t *pix_cols, int R, int N_rays, int patch_num, int patch_size,
+                      const float *sparse_depths, const float *sparse_weights, const float *dpt, int H, int W,
+                      float *terms5, float *d_rgb, float *d_depth, void *stream);
+
 /* ---- the step before the path: homography warp + variance cost volume -------------- */
 /* replaces utils/utils.py:1105-1172 (homo_warp) and the per-view loop of network/mvs_models.py:603-628.
  * B = 1.  depth_values [D][H+2pad][W+2pad] (already replicate-padded), matrices (src_proj @ ref_proj_inv)[:3]

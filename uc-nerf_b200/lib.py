@@ -89,6 +89,8 @@ _SIGS = {
     "ucn_frame_workspace_bytes": (C.c_size_t, [C.POINTER(Frame), C.c_int, C.c_int]),
     "ucn_render_rays": (C.c_int, [C.POINTER(Frame), C.POINTER(Weights), C.c_int, C.c_int, _fp, _fp, C.c_uint64,
                                   C.c_int, _fp, C.c_size_t, _fp, _fp, _fp]),
+    "ucn_render_losses": (C.c_int, [_fp, _fp, _fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, C.c_int,
+                                    C.c_int, _fp, _fp, _fp, _fp]),
     "ucn_homo_warp": (C.c_int, [_fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp]),
     "ucn_cost_volume_variance": (C.c_int, [_fp, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp, C.c_int, C.c_int, C.c_int,
                                            _fp, _fp]),

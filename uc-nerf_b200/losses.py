@@ -68,3 +68,43 @@ def render_losses(rgb, depth_pred, target_s, pix, N_rays, patch_num, patch_size,
     img = img2mse(rgb, target_s)
     loss = nerf_depth * 0.05 + smooth * 0.05 + scale_inv * 0.008 + img * 5.0
     return loss, {"img": img, "nerf_depth": nerf_depth, "smooth": smooth, "scale_invariant": scale_inv}
+
+
+class _FusedLossFn(torch.autograd.Function):
+    """loss and d loss / d (rgb, depth) from ONE launch (ucn_render_losses); backward only scales the saved gradients."""
+
+    @staticmethod
+    def forward(ctx, rgb, depth_pred, target_s, pix, N_rays, patch_num, patch_size, sparse_depths, sparse_weights, dpt):
+        import ctypes as C
+        from . import lib as L
+        lib = L.load()
+        R = rgb.shape[0]
+        H, W = dpt.shape[-2:]
+        f = lambda t: t.detach().to(torch.float32).contiguous()
+        rgb_c, dep_c, tgt_c = f(rgb), f(depth_pred), f(target_s)
+        rows, cols = pix[0].to(torch.int64).contiguous(), pix[1].to(torch.int64).contiguous()
+        terms = torch.empty(5, device=rgb.device, dtype=torch.float32)
+        d_rgb, d_depth = torch.empty_like(rgb_c), torch.empty_like(dep_c)
+        L.check(lib.ucn_render_losses(L.ptr(rgb_c), L.ptr(dep_c), L.ptr(tgt_c), C.c_void_p(rows.data_ptr()),
+                                      C.c_void_p(cols.data_ptr()), R, int(N_rays), int(patch_num), int(patch_size),
+                                      L.ptr(f(sparse_depths)), L.ptr(f(sparse_weights)), L.ptr(f(dpt)), int(H), int(W),
+                                      L.ptr(terms), L.ptr(d_rgb), L.ptr(d_depth), L.stream_ptr()), "ucn_render_losses")
+        ctx.save_for_backward(d_rgb, d_depth)
+        ctx.mark_non_differentiable(terms)
+        return terms[0].clone(), terms
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_terms):
+        d_rgb, d_depth = ctx.saved_tensors
+        return g_loss * d_rgb, g_loss * d_depth, None, None, None, None, None, None, None, None
+
+
+def render_losses_fused(rgb, depth_pred, target_s, pix, N_rays, patch_num, patch_size, sparse_depths, sparse_weights, dpt):
+    """Same contract as `render_losses`, one CUDA launch for the value and the gradient (CUDA tensors only; no CPU
+    path).  -> (loss, dict of terms)."""
+    if not rgb.is_cuda:
+        from .lib import UcnError
+        raise UcnError("render_losses_fused: CUDA tensors only (use render_losses for the torch glue)")
+    loss, t = _FusedLossFn.apply(rgb, depth_pred, target_s, pix, N_rays, patch_num, patch_size, sparse_depths,
+                                 sparse_weights, dpt)
+    return loss, {"img": t[1], "nerf_depth": t[2], "smooth": t[3], "scale_invariant": t[4]}
