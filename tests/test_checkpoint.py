@@ -83,7 +83,7 @@ def test_render_from_checkpoint_matches_golden(tmp_path):
                 'network_mvs_state_dict': {}}, p)
     m = make_model(c["V"] + 1).cuda().eval()
     checkpoint.load_ckpt(p, m)
-    fr = PackedFrame.from_scene(c["scene"], c["S"], "cuda:0")
+    fr = PackedFrame.from_scene(c["scene"], c["S"], "cuda:0", dir_switch=c["chunk"])   # golden was rendered in chunks (Q4)
     rgb, depth = FrameRenderer(fr, m.packed(), "fp32").render(t_rand=torch.from_numpy(c["t_rand"]).cuda())
     assert np.abs(rgb.cpu().numpy() - c["g"]["rgb"]).max() <= 1e-4
     assert np.abs(depth.cpu().numpy() - c["g"]["depth"]).max() <= 1e-4

@@ -29,10 +29,21 @@ def _dev(x, device) -> torch.Tensor:
     return x.detach().to(device=device, dtype=torch.float32).contiguous()
 
 
+_T_VALS: Dict = {}
+
+
 def linspace01(n: int, device) -> torch.Tensor:
     """t_vals exactly as the reference builds them: torch.linspace on the CPU, then .to(device)
-    (utils/utils.py:394)."""
-    return torch.linspace(0., 1., steps=n).to(device)
+    (utils/utils.py:394).  Cached per (n, device) and read-only: the pageable host->device copy behind .to()
+    synchronises the stream, which would drain the GPU once per frame of a sweep."""
+    device = torch.device(device)
+    if device.type == "cuda" and device.index is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    key = (int(n), str(device))
+    t = _T_VALS.get(key)
+    if t is None:
+        t = _T_VALS[key] = torch.linspace(0., 1., steps=n).to(device)
+    return t
 
 
 class PackedFrame:
