@@ -1,9 +1,10 @@
-"""Renderer-side loss terms of the training step (train.py:164-190) -- host-side glue in PyTorch.
+"""Renderer-side loss terms of the training step (train.py:164-190), SURVEY.md 8f rank 3.
 
-These are the terms of the reference's loss that act on the renderer's outputs (rgb, depth of the selected rays); they
-run on ~2 048 rays and 50 4x4 patches, so they stay elementwise torch code (SURVEY.md 8f rank 3 lists fusing them as
-a later row).  `cas_mvsnet_loss` (network/mvs_models.py:504-530) acts on the encoder's outputs and is not part of
-this path.
+These are the terms of the reference's loss that act on the renderer's outputs (rgb, depth of the selected rays), on
+~2 048 rays and 50 4x4 patches.  `render_losses_fused` is the product path: ONE launch of `ucn_render_losses`
+(csrc/ucn_losses.cu) returns every term and the closed-form gradient d loss / d (rgb, depth), CUDA tensors only.
+`render_losses` states the same contract as elementwise torch code (the mirror the tests pin to the reference's loss
+modules).  `cas_mvsnet_loss` (network/mvs_models.py:504-530) acts on the encoder's outputs and is not part of this path.
 
     utils/utils.py:11-12         img2mse, mse2psnr
     network/mvs_models.py:491-509 EdgePreservingSmoothnessLoss  -> edge_preserving_smoothness
