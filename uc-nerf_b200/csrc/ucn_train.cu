@@ -10,6 +10,11 @@
 // with two implementations: gemm_tc_kernel (tcgen05, split-bf16 operands converted on the fly, fp32 accumulation in
 // TMEM) for every product that fills a 128-wide tile, and gemm_kernel (fp32 CUDA cores) for the 3- and 1-wide heads.
 // The training batch is 2 048 rays (258 K samples, ~0.2 TFLOP per step), two orders of magnitude below a rendered frame.
+#include <stdlib.h>
+
+#include <mutex>
+#include <vector>
+
 #include "ucn_common.cuh"
 #include "ucn_tc.cuh"
 
@@ -104,15 +109,16 @@ __device__ __forceinline__ void split3(float a, float b, uint32_t (&w)[3]) {
 __global__ void __launch_bounds__(256)
 gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const float *__restrict__ B, long long sbp,
                long long sbj, float *__restrict__ C, long long ldc, const float *__restrict__ bias, int I, int J,
-               long long P, long long p_chunk, int flags, int a_vec, int b_vec) {
+               long long P, long long p_chunk, int flags, int a_vec, int b_vec, const unsigned char *__restrict__ bsplit) {
   extern __shared__ __align__(1024) unsigned char tc_smem[];
   const uint32_t sbase = smem_u32(tc_smem);
-  const uint32_t bar_done = sbase + 2 * TC_STAGE, tmem_slot = bar_done + 16;
+  const uint32_t bar_done = sbase + 2 * TC_STAGE, tmem_slot = bar_done + 16, bar_b = bar_done + 32;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int i0 = blockIdx.x * 128, j0 = blockIdx.y * 128;
+  const int j0 = blockIdx.y * 128, n_tile_i = (I + 127) / 128;
   const long long p_begin = (long long)blockIdx.z * p_chunk, p_end = min(P, p_begin + p_chunk);
   if (tid == 0) {
     mbar_init(bar_done, 1); mbar_init(bar_done + 8, 1);
+    mbar_init(bar_b, 1); mbar_init(bar_b + 8, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -125,10 +131,18 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(tc_smem + 2 * TC_STAGE + 16);
   const uint32_t idesc = umma_idesc_bf16(128);
   const int row = tid & 127, half = tid >> 7;                 // this thread stages k = 16*half .. 16*half+15 of its row
-  const bool a_ok = i0 + row < I, b_ok = j0 + row < J;
+  const bool b_ok = j0 + row < J;
   const int n_iter = (int)((p_end - p_begin + TC_SLAB - 1) / TC_SLAB);
-  for (int it = 0; it < n_iter; ++it) {
-    const int st = it & 1;
+  // Persistent over the row tiles of the output (grid.x CTAs stride over them): TMEM allocation, barrier set-up and
+  // CTA launch are paid once per CTA instead of once per tile (an empty tile pass of the one-tile-per-CTA form cost
+  // 41 of the 145 us of an M = 258 048, K = 128 forward product).  `git` counts slabs across tiles: the two stages
+  // and their barriers keep alternating through tile boundaries.
+  uint32_t git = 0;
+  for (int ti = blockIdx.x; ti < n_tile_i; ti += gridDim.x) {
+  const int i0 = ti * 128;
+  const bool a_ok = i0 + row < I;
+  for (int it = 0; it < n_iter; ++it, ++git) {
+    const int st = git & 1;
     const long long ps = p_begin + (long long)it * TC_SLAB, p0 = ps + 16 * half;
     // Operand slabs [128 rows x 32 p].  Two staging patterns per operand:
     //   vec    (p contiguous, 16-byte aligned rows): lanes sweep p, one float4 per lane -> four full 128-byte lines per
@@ -154,7 +168,9 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
 #pragma unroll
       for (int k = 0; k < 16; ++k) va[k] = (a_ok && p0 + k < p_end) ? A[(long long)(i0 + row) * sai + (p0 + k) * sap] : 0.0f;
     }
-    if (b_vec) {
+    if (bsplit) {
+      // B (the layer's weight matrix) was split once for the whole launch (split_b_kernel): its slab is a plain copy
+    } else if (b_vec) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int f = tid + 256 * q, r = f >> 3, c4 = f & 7;
@@ -171,10 +187,15 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
 #pragma unroll
       for (int k = 0; k < 16; ++k) vb[k] = (b_ok && p0 + k < p_end) ? B[(p0 + k) * sbp + (long long)(j0 + row) * sbj] : 0.0f;
     }
-    if (it >= 2) mbar_wait(bar_done + 8 * st, (uint32_t)(((it >> 1) - 1) & 1));     // MMAs of slab it-2 have read this stage
+    if (git >= 2) mbar_wait(bar_done + 8 * st, ((git >> 1) - 1) & 1);     // MMAs of slab git-2 have read this stage
     const uint32_t stage = sbase + st * TC_STAGE;
+    if (bsplit && tid == 0) {
+      mbar_expect_tx(bar_b + 8 * st, TC_OPER);
+      bulk_g2s(stage + TC_OPER, bsplit + ((size_t)blockIdx.y * n_iter + it) * TC_OPER, TC_OPER, bar_b + 8 * st);
+    }
 #pragma unroll
     for (int op = 0; op < 2; ++op) {
+      if (op == 1 && bsplit) break;
       const uint32_t base = stage + op * TC_OPER;
       if (op == 0 ? a_vec : b_vec) {
 #pragma unroll
@@ -206,6 +227,7 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
     tc_fence_before();
     __syncthreads();
     if (tid == 0) {
+      if (bsplit) mbar_wait(bar_b + 8 * st, (git >> 1) & 1);
       tc_fence_after();
       const uint32_t a0 = sbase + st * TC_STAGE, b0 = a0 + TC_OPER;
 #pragma unroll
@@ -227,8 +249,8 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
     }
   }
   {
-    const int last = n_iter - 1;
-    mbar_wait(bar_done + 8 * (last & 1), (uint32_t)((last >> 1) & 1));
+    const uint32_t last = git - 1;
+    mbar_wait(bar_done + 8 * (last & 1), (last >> 1) & 1);
     tc_fence_after();
   }
   // ---- epilogue: warp w reads TMEM lanes 32*(w%4).., columns 64*(w/4).. (thread = row), transposes 32 x 32 blocks
@@ -265,14 +287,41 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
       __syncwarp();
     }
   }
+  // the next tile overwrites the accumulator and the shared-memory tiles the epilogue has just read (its B slab
+  // arrives through the async proxy: order it after these generic-proxy accesses)
+  fence_async_smem();
   tc_fence_before();
   __syncthreads();
+  tc_fence_after();
+  }
   if (warp == 0) {
-    tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
   }
 }
 
+// The weight operand of a forward / grad-input product is the same for every 128-row tile: it is split ONCE per
+// launch into the three bf16 parts, already in the shared-memory image of a B slab ([part][K-chunk][row][8]), so
+// that the GEMM's CTAs fetch it with one bulk copy per slab instead of each re-converting it (half of the staging
+// instructions of those CTAs).  block = (slab, 128-column tile of the output), thread = (row, 16 reduction elements).
+__global__ void __launch_bounds__(256)
+split_b_kernel(const float *__restrict__ B, long long sbp, long long sbj, int J, long long P, int n_iter,
+               unsigned char *__restrict__ out) {
+  const int it = blockIdx.x, row = threadIdx.x & 127, half = threadIdx.x >> 7;
+  const long long j = (long long)blockIdx.y * 128 + row, p0 = (long long)it * TC_SLAB + 16 * half;
+  float v[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) v[k] = (j < J && p0 + k < P) ? B[(p0 + k) * sbp + j * sbj] : 0.0f;
+  unsigned char *dst = out + ((size_t)blockIdx.y * n_iter + it) * TC_OPER + row * 16 + (2 * half) * TC_CHUNK;
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    uint32_t w[4][3];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) split3(v[8 * c + 2 * q], v[8 * c + 2 * q + 1], w[q]);
+#pragma unroll
+    for (int pt = 0; pt < TC_PARTS; ++pt)
+      *reinterpret_cast<uint4 *>(dst + c * TC_CHUNK + pt * TC_PART) = make_uint4(w[0][pt], w[1][pt], w[2][pt], w[3][pt]);
+  }
+}
 
 // ---- the 3- and 1-wide heads (confi_rgb / alpha_1 / rgb / alpha, network/models.py:161-162,170,174) ------------------
 // A 64- or 128-wide GEMM tile would be >95 % padding there; these three kernels stream the wide operand once, coalesced.
@@ -607,6 +656,25 @@ skinny_bwd_input_v4_kernel(const float *__restrict__ dY, long long ldy, const fl
 
 inline unsigned nblk(long long n, int t) { return (unsigned)((n + t - 1) / t); }
 
+// scratch for the pre-split weight operand, one buffer per (device, stream): launches on one stream are ordered, so
+// the next product may overwrite it
+constexpr size_t kSplitBytes = 1u << 20;
+unsigned char *split_scratch(void *stream) {
+  struct Ent { int dev; void *stream; unsigned char *buf; };
+  static std::mutex mu;
+  static std::vector<Ent> tab;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lk(mu);
+  for (const Ent &e : tab) if (e.dev == dev && e.stream == stream) return e.buf;
+  if (tab.size() >= 16) return nullptr;                     // many streams: the remaining ones convert in the CTAs
+  void *p = nullptr;
+  if (cudaMalloc(&p, kSplitBytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  tab.push_back({dev, stream, static_cast<unsigned char *>(p)});
+  return static_cast<unsigned char *>(p);
+}
+
+int g_gemm_dbg = getenv("UCN_GEMM_DBG") ? atoi(getenv("UCN_GEMM_DBG")) : 0;   // EXPERIMENT: 16 no pre-split B, 32 one tile per CTA
 int launch_gemm(const float *A, long long sai, long long sap, const float *B, long long sbp, long long sbj, float *C,
                 long long ldc, const float *bias, long long I, long long J, long long P, int flags, int splits,
                 void *stream) {
@@ -634,7 +702,22 @@ int launch_gemm(const float *A, long long sai, long long sap, const float *B, lo
     const long long P4 = (P + 3) & ~3ll;
     const int a_vec = sap == 1 && splits == 1 && (reinterpret_cast<uintptr_t>(A) & 15) == 0 && (sai & 3) == 0 && P4 <= sai;
     const int b_vec = sbp == 1 && splits == 1 && (reinterpret_cast<uintptr_t>(B) & 15) == 0 && (sbj & 3) == 0 && P4 <= sbj;
-    gemm_tc_kernel<<<grid, 256, TC_SMEM, (cudaStream_t)stream>>>(A, sai, sap, B, sbp, sbj, C, ldc, bias, (int)I, (int)J, P, p_chunk, flags, a_vec, b_vec);
+    // B is a weight matrix shared by many row tiles (forward, grad-input): split it once (split_b_kernel)
+    const int n_iter = (int)((P + TC_SLAB - 1) / TC_SLAB);
+    unsigned char *bsplit = nullptr;
+    if (splits == 1 && grid.x >= 8 && (size_t)grid.y * n_iter * TC_OPER <= kSplitBytes) bsplit = split_scratch(stream);
+    if (bsplit) {
+      split_b_kernel<<<dim3((unsigned)n_iter, grid.y), 256, 0, (cudaStream_t)stream>>>(B, sbp, sbj, (int)J, P, n_iter, bsplit);
+      UCN_LAUNCH_CHECK("split_b_kernel");
+    }
+    if (!(g_gemm_dbg & 32)) {
+      int dev = 0, sms = 148;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      const unsigned cap = (unsigned)(2 * sms) / grid.y / grid.z;             // two CTAs per SM are resident
+      if (cap >= 1 && grid.x > cap) grid.x = cap;
+    }
+    gemm_tc_kernel<<<grid, 256, TC_SMEM, (cudaStream_t)stream>>>(A, sai, sap, B, sbp, sbj, C, ldc, bias, (int)I, (int)J, P, p_chunk, flags, a_vec, b_vec, (g_gemm_dbg & 16) ? nullptr : bsplit);
     UCN_LAUNCH_CHECK("gemm_tc_kernel");
     return UCN_OK;
   }
@@ -645,6 +728,7 @@ int launch_gemm(const float *A, long long sai, long long sap, const float *B, lo
 
 }  // namespace
 
+extern "C" int ucn_debug_gemm_flags(int f) { g_gemm_dbg = f; return 0; }
 // 0: nn.Linear products on tcgen05 (split-bf16, fp32 accumulate) where the shape fills a tile; 1: fp32 CUDA cores only
 extern "C" int ucn_train_gemm_mode(int mode) {
   UCN_CHECK_ARG(mode == 0 || mode == 1, "ucn_train_gemm_mode: 0 (tensor cores) or 1 (SIMT fp32)");
