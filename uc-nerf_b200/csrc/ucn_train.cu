@@ -10,8 +10,6 @@
 // with two implementations: gemm_tc_kernel (tcgen05, split-bf16 operands converted on the fly, fp32 accumulation in
 // TMEM) for every product that fills a 128-wide tile, and gemm_kernel (fp32 CUDA cores) for the 3- and 1-wide heads.
 // The training batch is 2 048 rays (258 K samples, ~0.2 TFLOP per step), two orders of magnitude below a rendered frame.
-#include <stdlib.h>
-
 #include <mutex>
 #include <vector>
 
@@ -106,7 +104,7 @@ __device__ __forceinline__ void split3(float a, float b, uint32_t (&w)[3]) {
   w[2] = pack2(ra - bf_lo(w[1]), rb - bf_hi(w[1]));
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const float *__restrict__ B, long long sbp,
                long long sbj, float *__restrict__ C, long long ldc, const float *__restrict__ bias, int I, int J,
                long long P, long long p_chunk, int flags, int a_vec, int b_vec, const unsigned char *__restrict__ bsplit) {
@@ -137,20 +135,20 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
   // CTA launch are paid once per CTA instead of once per tile (an empty tile pass of the one-tile-per-CTA form cost
   // 41 of the 145 us of an M = 258 048, K = 128 forward product).  `git` counts slabs across tiles: the two stages
   // and their barriers keep alternating through tile boundaries.
-  uint32_t git = 0;
-  for (int ti = blockIdx.x; ti < n_tile_i; ti += gridDim.x) {
-  const int i0 = ti * 128;
-  const bool a_ok = i0 + row < I;
-  for (int it = 0; it < n_iter; ++it, ++git) {
-    const int st = git & 1;
+  // Operand slabs [128 rows x 32 p].  Two staging patterns per operand:
+  //   vec    (p contiguous, 16-byte aligned rows): lanes sweep p, one float4 per lane -> four full 128-byte lines per
+  //          warp instruction;
+  //   scalar (rows contiguous, or unaligned): thread = row, 16 p values each -- coalesced when the row index is the
+  //          contiguous one (grad-weight operands, grad-input weights), L1-cached otherwise (small weight matrices).
+  // The loads of the NEXT slab (the next tile's first slab at a tile boundary) are issued as soon as the current slab has
+  // been converted out of the same registers: they are in flight across the barrier, the MMA issue, the epilogue and
+  // the wait for the stage.
+  float va[16], vb[16];
+  float4 fa[4], fb[4];
+  auto load_slab = [&](int ti, int it) {
+    const int i0 = ti * 128;
+    const bool a_ok = i0 + row < I;
     const long long ps = p_begin + (long long)it * TC_SLAB, p0 = ps + 16 * half;
-    // Operand slabs [128 rows x 32 p].  Two staging patterns per operand:
-    //   vec    (p contiguous, 16-byte aligned rows): lanes sweep p, one float4 per lane -> four full 128-byte lines per
-    //          warp instruction;
-    //   scalar (rows contiguous, or unaligned): thread = row, 16 p values each -- coalesced when the row index is the
-    //          contiguous one (grad-weight operands, grad-input weights), L1-cached otherwise (small weight matrices).
-    float va[16], vb[16];
-    float4 fa[4], fb[4];
     if (a_vec) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
@@ -187,6 +185,13 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
 #pragma unroll
       for (int k = 0; k < 16; ++k) vb[k] = (b_ok && p0 + k < p_end) ? B[(p0 + k) * sbp + (long long)(j0 + row) * sbj] : 0.0f;
     }
+  };
+  uint32_t git = 0;
+  if ((int)blockIdx.x < n_tile_i) load_slab(blockIdx.x, 0);
+  for (int ti = blockIdx.x; ti < n_tile_i; ti += gridDim.x) {
+  const int i0 = ti * 128;
+  for (int it = 0; it < n_iter; ++it, ++git) {
+    const int st = git & 1;
     if (git >= 2) mbar_wait(bar_done + 8 * st, ((git >> 1) - 1) & 1);     // MMAs of slab git-2 have read this stage
     const uint32_t stage = sbase + st * TC_STAGE;
     if (bsplit && tid == 0) {
@@ -222,6 +227,11 @@ gemm_tc_kernel(const float *__restrict__ A, long long sai, long long sap, const 
           for (int pt = 0; pt < TC_PARTS; ++pt) sts128(sa + c * TC_CHUNK + pt * TC_PART, w[0][pt], w[1][pt], w[2][pt], w[3][pt]);
         }
       }
+    }
+    {
+      int nti = ti, nit = it + 1;
+      if (nit == n_iter) { nti = ti + (int)gridDim.x; nit = 0; }
+      if (nti < n_tile_i) load_slab(nti, nit);
     }
     fence_async_smem();
     tc_fence_before();
@@ -674,7 +684,7 @@ unsigned char *split_scratch(void *stream) {
   return static_cast<unsigned char *>(p);
 }
 
-int g_gemm_dbg = getenv("UCN_GEMM_DBG") ? atoi(getenv("UCN_GEMM_DBG")) : 0;   // EXPERIMENT: 16 no pre-split B, 32 one tile per CTA
+int g_gemm_dbg = 0;   // timing switches for tools/ubench_gemm.py: 16 no pre-split B, 32 one tile per CTA (results unchanged)
 int launch_gemm(const float *A, long long sai, long long sap, const float *B, long long sbp, long long sbj, float *C,
                 long long ldc, const float *bias, long long I, long long J, long long P, int flags, int splits,
                 void *stream) {
@@ -728,6 +738,7 @@ int launch_gemm(const float *A, long long sai, long long sap, const float *B, lo
 
 }  // namespace
 
+// debug aid (A/B timing of the staging variants of gemm_tc_kernel; every variant computes the same product)
 extern "C" int ucn_debug_gemm_flags(int f) { g_gemm_dbg = f; return 0; }
 // 0: nn.Linear products on tcgen05 (split-bf16, fp32 accumulate) where the shape fills a tile; 1: fp32 CUDA cores only
 extern "C" int ucn_train_gemm_mode(int mode) {
