@@ -359,3 +359,23 @@ def test_host_sweep_matches_frame_renderer():
             cur["sc"] = scenes[i + 1]
             sweep2.submit(i + 1, maps[i + 1], maps[i + 2] if i + 2 < len(scenes) else None, seed=7)
         assert torch.equal(sweep2.result(i), want[i]), i
+
+
+def test_host_copy_cache_follows_the_tensor():
+    """Camera tensors reach the kernels by value through a cached host copy (frame._host_copy): the cache is keyed by
+    tensor identity + view geometry and invalidated by `_version`, so in-place writes, views and new tensors (possibly at
+    a recycled device address) must all be seen."""
+    from ucnerf_b200 import frame
+    t = torch.eye(4, device=DEV)
+    assert frame._host(t)[0, 0] == 1.0 and frame._host(t) is frame._host(t)          # second read: cached, no sync
+    t[0, 0] = 5.0
+    assert frame._host(t)[0, 0] == 5.0                                               # in-place write bumps _version
+    assert frame._host(t[1])[1] == 1.0
+    t.mul_(2.0)
+    assert frame._host(t[1])[1] == 2.0 and frame.host_scalar(t[0, 0]) == 10.0        # views share the version counter
+    with pytest.raises(ValueError):
+        frame._host_copy(t)[0, 0] = 0.0                                              # cached arrays are read-only
+    for k in range(4):                                                               # fresh tensors, recycled storage
+        u = torch.full((4, 4), float(k), device=DEV)
+        assert frame._host(u).sum() == 16.0 * k
+        del u

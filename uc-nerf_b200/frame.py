@@ -6,6 +6,7 @@ PyTorch is used for device memory and streams only; all arithmetic happens in li
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 from typing import Dict, Optional, Sequence
 
 import numpy as np
@@ -16,11 +17,40 @@ from . import lib as L
 STAGES = ("stage1", "stage2", "stage3")
 
 
+_HOST_COPIES: Dict = {}
+
+
+def _host_copy(x: torch.Tensor) -> np.ndarray:
+    """Host copy of a small device tensor (camera matrices, near / far) that the kernels take BY VALUE.  The
+    device->host read behind it synchronises the stream, and a training step that rebuilds its frame every step pays
+    eight of them; the copy is therefore cached per tensor OBJECT: key = identity of the base tensor (weak reference,
+    so a new tensor at a recycled address never hits) + view geometry, valid while `_version` is unchanged (every
+    in-place write bumps it).  The cached array is read-only."""
+    base = x._base if x._base is not None else x
+    key = (id(base), x.storage_offset(), tuple(x.shape), tuple(x.stride()), x.dtype)
+    hit = _HOST_COPIES.get(key)
+    if hit is not None and hit[0]() is base and hit[1] == x._version:
+        return hit[2]
+    a = x.detach().to("cpu", torch.float32).contiguous().numpy()
+    a.setflags(write=False)
+    if len(_HOST_COPIES) >= 256:
+        _HOST_COPIES.clear()
+    _HOST_COPIES[key] = (weakref.ref(base), x._version, a)
+    return a
+
+
 def _host(x, shape=None) -> np.ndarray:
     if isinstance(x, torch.Tensor):
-        x = x.detach().to("cpu", torch.float32).numpy()
+        x = _host_copy(x) if x.is_cuda else x.detach().to(torch.float32).numpy()
     a = np.ascontiguousarray(np.asarray(x, dtype=np.float32))
     return a if shape is None else a.reshape(shape)
+
+
+def host_scalar(x) -> float:
+    """float(x) without a stream synchronisation when x is a device tensor whose host copy is cached."""
+    if isinstance(x, torch.Tensor) and x.is_cuda:
+        return float(_host_copy(x).reshape(-1)[0])
+    return float(x)
 
 
 def _dev(x, device) -> torch.Tensor:
@@ -72,7 +102,7 @@ class PackedFrame:
         c.c2w[:] = _host(c2w, (4, 4)).reshape(-1).tolist()
         w2c = _host(w2c, (4, 4))
         c.w2c[:] = w2c.reshape(-1).tolist()
-        c.near, c.far = float(near), float(far)
+        c.near, c.far = host_scalar(near), host_scalar(far)
         r0 = w2c[:3, :3] if dir_rot0 is None else _host(dir_rot0)[:3, :3]
         r1 = r0 if dir_rot1 is None else _host(dir_rot1)[:3, :3]
         c.dir_rot0[:] = np.ascontiguousarray(r0).reshape(-1).tolist()

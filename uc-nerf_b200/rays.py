@@ -20,7 +20,7 @@ import torch
 
 from . import lib as L
 from . import train_path as _tp
-from .frame import PackedFrame, linspace01
+from .frame import PackedFrame, _host, host_scalar, linspace01
 
 _FRAME_CACHE: Dict[tuple, PackedFrame] = {}
 _CACHE_MAX = 8
@@ -50,7 +50,7 @@ def sample_points_uniform(device, near, far, num_samples, num_rays):
 
 def _rays_frame(H, W, S, tgt_to_world, world_to_ref, intrinsic, near, far, outputs) -> PackedFrame:
     dvs = [outputs[s]["depth_values"] for s in ("stage1", "stage2", "stage3")]
-    key = ("rays", H, W, S, float(near), float(far)) + _key(tgt_to_world, world_to_ref, intrinsic, *dvs)
+    key = ("rays", H, W, S, host_scalar(near), host_scalar(far)) + _key(tgt_to_world, world_to_ref, intrinsic, *dvs)
     fr = _FRAME_CACHE.get(key)
     if fr is None:
         fr = PackedFrame(tgt_to_world.device)
@@ -74,7 +74,7 @@ def build_rays_test(H, W, tgt_to_world, world_to_ref, intrinsic, near_fars_ref, 
     device = tgt_to_world.device
     S = int(N_samples)
     near, far = near_fars_ref[ref_idx, 0], near_fars_ref[ref_idx, 1]
-    fr = _rays_frame(int(H), int(W), S, tgt_to_world, world_to_ref, intrinsic, float(near), float(far), outputs)
+    fr = _rays_frame(int(H), int(W), S, tgt_to_world, world_to_ref, intrinsic, host_scalar(near), host_scalar(far), outputs)
     total = H * W
     lo, hi = (0, total) if chunk <= 0 else (idx * chunk, min(total, (idx + 1) * chunk))
     R = hi - lo
@@ -167,8 +167,8 @@ def get_ndc_coordinate(w2c_ref, intrinsic_ref, point_samples, inv_scale, near_fa
     R, S = point_samples.shape[:2]
     pts = point_samples.to(torch.float32).contiguous()
     out = torch.empty((R, S, 3), device=pts.device)
-    w2c = (C.c_float * 16)(*torch.as_tensor(w2c_ref).detach().float().cpu().reshape(-1).tolist())
-    K = (C.c_float * 9)(*torch.as_tensor(intrinsic_ref).detach().float().cpu().reshape(-1).tolist())
+    w2c = (C.c_float * 16)(*_host(torch.as_tensor(w2c_ref)).reshape(-1).tolist())
+    K = (C.c_float * 9)(*_host(torch.as_tensor(intrinsic_ref)).reshape(-1).tolist())
     Wm1, Hm1 = (int(v) for v in torch.as_tensor(inv_scale).reshape(-1).tolist())
     L.check(L.load().ucn_project_points(w2c, K, Hm1 + 1, Wm1 + 1, L.ptr(pts), R * S, L.ptr(out), L.stream_ptr()),
             "ucn_project_points")
@@ -308,7 +308,7 @@ def build_rays(args, imgs, mvs_confidence, sparse_depths, coords, pose_ref, w2cs
     R = pix.shape[1]
     w2c_ref, intrinsic_ref = pose_ref['w2cs'][ref_idx], pose_ref['intrinsics'][ref_idx]
     near, far = pose_ref['near_fars'][ref_idx, 0], pose_ref['near_fars'][ref_idx, 1]
-    fr = _rays_frame(int(H), int(W), S, c2ws[0], w2c_ref, intrinsics[0], float(near), float(far), outputs)
+    fr = _rays_frame(int(H), int(W), S, c2ws[0], w2c_ref, intrinsics[0], host_scalar(near), host_scalar(far), outputs)
     z = torch.empty((R, S), device=device)
     rays_d = torch.empty((R, 3), device=device)
     pts = torch.empty((R, S, 3), device=device)

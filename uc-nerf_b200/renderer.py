@@ -18,7 +18,7 @@ import torch
 from . import lib as L
 from . import rays as _rays
 from . import train_path as _tp
-from .frame import PackedFrame
+from .frame import PackedFrame, _host
 
 
 def depth2dist(z_vals, cos_angle):
@@ -74,7 +74,7 @@ def _dir_feature(w2c_ref, rays_dir, normalize=True):
     if not normalize:      # reference signature: already-normalised directions; one tiny matmul, not a hot op
         return rays_dir @ w2c_ref[:3, :3].t()
     fr = PackedFrame(rays_dir.device)
-    rot = w2c_ref.detach().float().cpu().numpy()[:3, :3]
+    rot = _host(w2c_ref)[:3, :3]
     fr.c.dir_rot0[:] = rot.reshape(-1).tolist()
     fr.c.dir_rot1[:] = rot.reshape(-1).tolist()
     fr.c.dir_switch = 2 ** 31 - 1
