@@ -207,7 +207,14 @@ class MlpFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, d_raw):
-        G = {n: torch.zeros_like(p) for n, p in ctx.P.items()}
+        # every parameter gradient is a view of ONE zero-filled buffer (one fill launch instead of 30); offsets are
+        # multiples of four floats so that the 16-byte kernel variants still apply
+        offs, total = {}, 0
+        for n, p in ctx.P.items():
+            offs[n] = total
+            total += (p.numel() + 3) & ~3
+        flat = torch.zeros((total,), device=d_raw.device, dtype=torch.float32)
+        G = {n: flat[offs[n]:offs[n] + p.numel()].view(p.shape) for n, p in ctx.P.items()}
         d_feat = mlp_backward(CudaOps(), ctx.P, ctx.saved, d_raw.to(torch.float32).reshape(-1, 4).contiguous(), G)
         ctx.saved = None
         return (None, None, d_feat.reshape(ctx.shape), None) + tuple(G[n] for n in PARAM_NAMES)
@@ -281,21 +288,14 @@ def allreduce_grads(params, world_size: int, bucket: "torch.Tensor | None" = Non
     n = sum(p.numel() for p in params)
     if bucket is None or bucket.numel() != n:
         bucket = torch.empty((n,), device=params[0].device, dtype=torch.float32)
-    o = 0
-    for p in params:
-        k = p.numel()
-        if p.grad is None:
-            bucket[o:o + k].zero_()
-        else:
-            bucket[o:o + k].copy_(p.grad.reshape(-1))
-        o += k
+    # pack: ONE concatenation kernel into the bucket (not one copy per parameter); unpack: one fused multi-tensor copy
+    pieces = [p.grad.reshape(-1).to(torch.float32) if p.grad is not None else bucket.new_zeros(p.numel()) for p in params]
+    torch.cat(pieces, out=bucket)
     if world_size > 1:
         dist.all_reduce(bucket, op=dist.ReduceOp.SUM)
         bucket.div_(world_size)
-    o = 0
-    for p in params:
-        k = p.numel()
-        if p.grad is not None:
-            p.grad.copy_(bucket[o:o + k].view_as(p.grad))
-        o += k
+        chunks = bucket.split([p.numel() for p in params])
+        dst = [p.grad for p in params if p.grad is not None]
+        src = [c.view_as(p.grad) for c, p in zip(chunks, params) if p.grad is not None]
+        torch._foreach_copy_(dst, src)
     return bucket
