@@ -123,17 +123,25 @@ def mlp_forward_train(ops, P: Dict[str, torch.Tensor], ndc, angle, feat, S: int)
         ops.film_relu_fwd(PRE[i], MOD, out)
         x = PH[:, :191] if i == 4 else out
     BASE4, ADAPT4, HFB, VH, raw = new(M, 4), new(M, 4), new(M, 128), new(M, 128), new(M, 4)
-    ops.linear_fwd(H5, P["confi_rgb_linear.weight"], P["confi_rgb_linear.bias"], BASE4[:, :3])               # :161
-    ops.linear_fwd(H5, P["alpha_linear_1.weight"], P["alpha_linear_1.bias"], BASE4[:, 3:4])                  # :162
+    # base heads (:161-162) stacked into one 4-wide product: h is streamed once instead of twice
+    WB = torch.cat((P["confi_rgb_linear.weight"], P["alpha_linear_1.weight"]), 0)
+    ops.linear_fwd(H5, WB, torch.cat((P["confi_rgb_linear.bias"], P["alpha_linear_1.bias"]), 0), BASE4)
     ops.mul_fwd(H5, FB, HFB)
     ops.linear_fwd(HFB, P["feature_linear.weight"], P["feature_linear.bias"], FTV[:, :128])                  # :164
-    ops.linear_fwd(FTV[:, :155], P["views_linears.0.weight"], P["views_linears.0.bias"], VH[:, :64], relu=True)            # :168-169
-    ops.linear_fwd(FTV[:, :155], P["view_confi_linears.0.weight"], P["view_confi_linears.0.bias"], VH[:, 64:], relu=True)  # :172-173
-    ops.linear_fwd(VH[:, :64], P["rgb_linear.weight"], P["rgb_linear.bias"], ADAPT4[:, :3])                  # :170
-    ops.linear_fwd(VH[:, 64:], P["alpha_linear.weight"], P["alpha_linear.bias"], ADAPT4[:, 3:4])             # :174
+    # the two 155 -> 64 view branches (:168-169, :172-173) read the same input: one 128-wide product on the stacked
+    # weights fills the 128 x 128 tensor-core tile that each 64-wide product would leave half empty
+    WV = torch.cat((P["views_linears.0.weight"], P["view_confi_linears.0.weight"]), 0)
+    BV = torch.cat((P["views_linears.0.bias"], P["view_confi_linears.0.bias"]), 0)
+    ops.linear_fwd(FTV[:, :155], WV, BV, VH, relu=True)
+    # adapt heads (:170, :174): rgb reads columns 0..63 of VH, alpha columns 64..127 -- one 4-wide product on the
+    # block matrix [[rgb_w, 0], [0, alpha_w]] (the zero blocks add exact zeros)
+    WA = WB.new_zeros((4, 128))
+    WA[:3, :64] = P["rgb_linear.weight"]
+    WA[3:, 64:] = P["alpha_linear.weight"]
+    ops.linear_fwd(VH, WA, torch.cat((P["rgb_linear.bias"], P["alpha_linear.bias"]), 0), ADAPT4)
     ops.blend_fwd(BASE4, ADAPT4, feat[:, F - 1:F], raw)                                                      # :149,177-180
     saved = dict(PH=PH, FTV=FTV, MOD=MOD, FB=FB, PRE=PRE, H=H, H5=H5, BASE4=BASE4, ADAPT4=ADAPT4, HFB=HFB, VH=VH,
-                 raw=raw, feat=feat)
+                 raw=raw, feat=feat, WV=WV, WB=WB, WA=WA)
     return raw, saved
 
 
@@ -151,23 +159,28 @@ def mlp_backward(ops, P: Dict[str, torch.Tensor], saved, d_raw, G: Dict[str, tor
     ops.blend_bwd(d_raw, s["raw"], s["BASE4"], s["ADAPT4"], feat[:, F - 1:F], dBASE4, dADAPT4, d_feat[:, F - 1:F])
     # adapt heads (models.py:170,174) and the two 155 -> 64 view branches (:168-173)
     dVH, dVPRE, dFT = new(M, 128), new(M, 128), new(M, 128)
-    ops.linear_bwd_input(dADAPT4[:, :3], P["rgb_linear.weight"], dVH[:, :64])
-    ops.linear_bwd_input(dADAPT4[:, 3:4], P["alpha_linear.weight"], dVH[:, 64:])
-    ops.linear_bwd_weight(dADAPT4[:, :3], VH[:, :64], G["rgb_linear.weight"], G["rgb_linear.bias"])
-    ops.linear_bwd_weight(dADAPT4[:, 3:4], VH[:, 64:], G["alpha_linear.weight"], G["alpha_linear.bias"])
+    WA, WB = s["WA"], s["WB"]
+    GA, GAb = torch.zeros_like(WA), WA.new_zeros(4)
+    ops.linear_bwd_input(dADAPT4, WA, dVH)
+    ops.linear_bwd_weight(dADAPT4, VH, GA, GAb)
+    G["rgb_linear.weight"].copy_(GA[:3, :64]); G["alpha_linear.weight"].copy_(GA[3:, 64:])
+    G["rgb_linear.bias"].copy_(GAb[:3]); G["alpha_linear.bias"].copy_(GAb[3:])
     ops.relu_bwd(dVH, VH, dVPRE)
-    ops.linear_bwd_input(dVPRE[:, :64], P["views_linears.0.weight"][:, :128], dFT)
-    ops.linear_bwd_input(dVPRE[:, 64:], P["view_confi_linears.0.weight"][:, :128], dFT, accumulate=True)
-    ops.linear_bwd_weight(dVPRE[:, :64], FTV[:, :155], G["views_linears.0.weight"], G["views_linears.0.bias"])
-    ops.linear_bwd_weight(dVPRE[:, 64:], FTV[:, :155], G["view_confi_linears.0.weight"], G["view_confi_linears.0.bias"])
+    WV = s["WV"]                                                       # stacked [views_linears.0 ; view_confi_linears.0]
+    ops.linear_bwd_input(dVPRE, WV[:, :128], dFT)
+    GWV, GBV = torch.zeros_like(WV), WV.new_zeros(128)
+    ops.linear_bwd_weight(dVPRE, FTV[:, :155], GWV, GBV)
+    G["views_linears.0.weight"].copy_(GWV[:64]); G["view_confi_linears.0.weight"].copy_(GWV[64:])
+    G["views_linears.0.bias"].copy_(GBV[:64]); G["view_confi_linears.0.bias"].copy_(GBV[64:])
     # feature_linear on h * feats_bias (:164), base heads (:161-162)
     dHFB, dH, dFB = new(M, 128), new(M, 128), new(M, 128)
     ops.linear_bwd_input(dFT, P["feature_linear.weight"], dHFB)
     ops.linear_bwd_weight(dFT, HFB, G["feature_linear.weight"], G["feature_linear.bias"])
-    ops.linear_bwd_input(dBASE4[:, :3], P["confi_rgb_linear.weight"], dH)
-    ops.linear_bwd_input(dBASE4[:, 3:4], P["alpha_linear_1.weight"], dH, accumulate=True)
-    ops.linear_bwd_weight(dBASE4[:, :3], H5, G["confi_rgb_linear.weight"], G["confi_rgb_linear.bias"])
-    ops.linear_bwd_weight(dBASE4[:, 3:4], H5, G["alpha_linear_1.weight"], G["alpha_linear_1.bias"])
+    GB, GBb = torch.zeros_like(WB), WB.new_zeros(4)
+    ops.linear_bwd_input(dBASE4, WB, dH)
+    ops.linear_bwd_weight(dBASE4, H5, GB, GBb)
+    G["confi_rgb_linear.weight"].copy_(GB[:3]); G["alpha_linear_1.weight"].copy_(GB[3:])
+    G["confi_rgb_linear.bias"].copy_(GBb[:3]); G["alpha_linear_1.bias"].copy_(GBb[3:])
     ops.mul_bwd(dHFB, H5, FB, dH, True, dFB)
     # the six FiLM-modulated layers, last to first (:153-157)
     dPRE, dMOD = new(M, 128), new(M, 128)
