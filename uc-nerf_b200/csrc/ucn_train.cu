@@ -436,15 +436,32 @@ __device__ __forceinline__ void embed(const float x[3], int L, float *out) {
     }
   }
 }
-__global__ void prep_kernel(const float *__restrict__ ndc, const float *__restrict__ angle, int S, long long N,
-                            float *__restrict__ ph, long long ldph, float *__restrict__ ftv, long long ldftv) {
-  const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= N) return;
-  const float x[3] = {ndc[3 * q], ndc[3 * q + 1], ndc[3 * q + 2]};
-  const long long r = q / S;
-  const float a[3] = {angle[3 * r], angle[3 * r + 1], angle[3 * r + 2]};
-  embed(x, 10, ph + q * ldph);              // PE(ndc)  -> ph[:, 0:63]
-  embed(a, 4, ftv + q * ldftv + 128);       // PE(dir)  -> ftv[:, 128:155]
+// thread = sample computes its 63 + 27 values into shared memory (odd pitch: conflict-free), then the block writes
+// the rows out with consecutive lanes on consecutive columns (a per-thread row write would touch one 32-byte sector
+// per lane and store instruction)
+constexpr int PREP_T = 128, PREP_LD = 91;
+__global__ void __launch_bounds__(PREP_T)
+prep_kernel(const float *__restrict__ ndc, const float *__restrict__ angle, int S, long long N,
+            float *__restrict__ ph, long long ldph, float *__restrict__ ftv, long long ldftv) {
+  __shared__ float sm[PREP_T * PREP_LD];
+  const long long q0 = (long long)blockIdx.x * PREP_T, q = q0 + threadIdx.x;
+  if (q < N) {
+    const float x[3] = {ndc[3 * q], ndc[3 * q + 1], ndc[3 * q + 2]};
+    const long long r = q / S;
+    const float a[3] = {angle[3 * r], angle[3 * r + 1], angle[3 * r + 2]};
+    embed(x, 10, sm + threadIdx.x * PREP_LD);              // PE(ndc)  -> ph[:, 0:63]
+    embed(a, 4, sm + threadIdx.x * PREP_LD + 63);          // PE(dir)  -> ftv[:, 128:155]
+  }
+  __syncthreads();
+  const int rows = (int)min((long long)PREP_T, N - q0);
+  for (int e = threadIdx.x; e < rows * 63; e += PREP_T) {
+    const int r = e / 63, c = e - 63 * r;
+    ph[(q0 + r) * ldph + c] = sm[r * PREP_LD + c];
+  }
+  for (int e = threadIdx.x; e < rows * 27; e += PREP_T) {
+    const int r = e / 27, c = e - 27 * r;
+    ftv[(q0 + r) * ldftv + 128 + c] = sm[r * PREP_LD + 63 + c];
+  }
 }
 
 __global__ void film_relu_fwd_kernel(const float *__restrict__ pre, const float *__restrict__ mod, float *__restrict__ h,
@@ -809,7 +826,7 @@ extern "C" int ucn_train_prep(const float *ndc, const float *angle, int S, int64
   UCN_CHECK_ARG(ndc && angle && ph && ftv && S > 0, "ucn_train_prep: bad argument");
   UCN_CHECK_ARG(ldph >= 63 && ldftv >= 155, "ucn_train_prep: leading dimensions");
   if (N <= 0) return UCN_OK;
-  prep_kernel<<<nblk(N, 128), 128, 0, (cudaStream_t)stream>>>(ndc, angle, S, N, ph, ldph, ftv, ldftv);
+  prep_kernel<<<nblk(N, PREP_T), PREP_T, 0, (cudaStream_t)stream>>>(ndc, angle, S, N, ph, ldph, ftv, ldftv);
   UCN_LAUNCH_CHECK("prep_kernel");
   return UCN_OK;
 }

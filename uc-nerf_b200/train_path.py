@@ -109,8 +109,10 @@ def mlp_forward_train(ops, P: Dict[str, torch.Tensor], ndc, angle, feat, S: int)
     V = (F - 25) // 12
     Kf, Kb = 24 + 4 * V, 8 * V
     new = lambda *shape: feat.new_empty(shape)
-    PH = feat.new_zeros((M, 192))          # [PE_10(ndc) 0..62 | h4 63..190 | pad]   (skip concat, models.py:156-157)
-    FTV = feat.new_zeros((M, 160))         # [feature 0..127 | PE_4(dir) 128..154 | pad]  (models.py:166)
+    # every column that is ever read (0..190 / 0..154) is written below; the pad columns only round the pitch up to a
+    # multiple of four floats and are masked out by the kernels, so the buffers need no zero fill
+    PH = new(M, 192)                       # [PE_10(ndc) 0..62 | h4 63..190 | pad]   (skip concat, models.py:156-157)
+    FTV = new(M, 160)                      # [feature 0..127 | PE_4(dir) 128..154 | pad]  (models.py:166)
     ops.prep(ndc, angle, S, PH, FTV)
     MOD, FB = new(M, 128), new(M, 128)
     ops.linear_fwd(feat[:, :Kf], P["pts_bias_depth_fine.weight"], P["pts_bias_depth_fine.bias"], MOD)       # :150
