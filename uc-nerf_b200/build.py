@@ -58,7 +58,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         fh.write("\n".join(logs))
     if verbose:
         print("\n".join(logs))
-    cmd = [nvcc, "-shared", "-o", OUT] + (["-ccbin", host_cc] if host_cc else []) + objs + []
+    cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT] + (["-ccbin", host_cc] if host_cc else []) + objs
     subprocess.run(cmd, check=True)
     return OUT
 
