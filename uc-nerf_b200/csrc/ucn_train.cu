@@ -813,6 +813,7 @@ extern "C" int ucn_linear_bwd_weight(const float *dY, int64_t ldy, const float *
   int splits = (int)((2 * 148 + tiles - 1) / tiles);
   const long long max_splits = (M + 255) / 256;
   if (splits > max_splits) splits = (int)max_splits;
+  if (g_gemm_dbg >> 8) splits = g_gemm_dbg >> 8;      // timing switch (tools/ubench_gemm.py)
   const int rc = launch_gemm(dY, 1, ldy, X, ldx, 1, dW, lddw, nullptr, N, K, M, G_ATOMIC, splits < 1 ? 1 : splits, stream);
   if (rc != UCN_OK || !db) return rc;
   const long long chunks = (M + 511) / 512;
