@@ -156,7 +156,7 @@ def mlp_backward(ops, P: Dict[str, torch.Tensor], saved, d_raw, G: Dict[str, tor
     V = (F - 25) // 12
     Kf, Kb = 24 + 4 * V, 8 * V
     new = lambda *shape: feat.new_empty(shape)
-    d_feat = feat.new_zeros((M, F))
+    d_feat = new(M, F)                     # columns [0,Kf) | [Kf,Kf+Kb) | F-1 are each written (not accumulated) below
     dBASE4, dADAPT4 = new(M, 4), new(M, 4)
     ops.blend_bwd(d_raw, s["raw"], s["BASE4"], s["ADAPT4"], feat[:, F - 1:F], dBASE4, dADAPT4, d_feat[:, F - 1:F])
     # adapt heads (models.py:170,174) and the two 155 -> 64 view branches (:168-173)
