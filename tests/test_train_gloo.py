@@ -89,3 +89,25 @@ def test_single_rank_is_identity():
     TP.allreduce_grads(params, 1)
     for p, n in zip([p for i, p in enumerate(params) if i != 5], TP.PARAM_NAMES):
         assert torch.equal(p.grad, G[n])
+
+
+def test_bucket_packs_views_of_a_flat_gradient_buffer():
+    """MlpFn.backward hands out parameter gradients as views of ONE padded buffer (offsets rounded up to four floats);
+    the bucket must hold their plain concatenation (no padding), zeros for a parameter without a gradient."""
+    shapes = [(3, 5), (7,), (2, 2, 3), (1,)]
+    offs, total = [], 0
+    for sh in shapes:
+        offs.append(total)
+        total += (int(np.prod(sh)) + 3) & ~3
+    flat = torch.arange(total, dtype=torch.float32) + 1.0
+    params = []
+    for sh, o in zip(shapes, offs):
+        p = torch.nn.Parameter(torch.zeros(sh))
+        p.grad = flat[o:o + int(np.prod(sh))].view(sh)
+        params.append(p)
+    params.insert(2, torch.nn.Parameter(torch.zeros(4)))               # never used: no gradient
+    bucket = TP.allreduce_grads(params, 1)
+    want = torch.cat([p.grad.reshape(-1) if p.grad is not None else torch.zeros(p.numel()) for p in params])
+    assert torch.equal(bucket, want) and bucket.numel() == sum(p.numel() for p in params)
+    again = TP.allreduce_grads(params, 1, bucket)
+    assert again is bucket and torch.equal(bucket, want)               # the bucket is reused across steps
