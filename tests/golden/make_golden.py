@@ -13,7 +13,7 @@ scenes of ucnerf_b200.synthetic, runs its eval loop verbatim --
 quirk Q4), and stores the outputs.  Inputs are NOT stored: they are regenerated from the seed.
 /root/reference does not exist on the GPU box; only the .npz files travel.
 
-Usage:  python tests/golden/make_golden.py            (rewrites tests/golden/*.npz)
+Usage:  python tests/golden/make_golden.py [case ...]  (rewrites tests/golden/<case>.npz; default: all cases)
 """
 import os
 import sys
@@ -34,6 +34,9 @@ CASES = {
     "small_v5": dict(H=16, W=24, V=5, S=15, chunk=128, seed=2, stride=4),
     "s126_v3": dict(H=16, W=20, V=3, S=126, chunk=160, seed=3, stride=16),
     "moved_v3": dict(H=16, W=20, V=3, S=12, chunk=100, seed=4, stride=4, target_motion=1.0),
+    # BASELINE config 5's sample / view counts (S=255 -> 85-long stage sweeps, V'=5 -> F=85) on a tiny frame, two
+    # chunks so that the dir-frame switch (quirk Q4) falls inside
+    "s255_v5": dict(H=8, W=12, V=5, S=255, chunk=48, seed=5, stride=8),
 }
 
 
@@ -170,8 +173,10 @@ def main():
     # side pins used by the oracle's arithmetic model
     lin = {str(n): torch.linspace(0., 1., n).numpy() for n in (1, 2, 3, 4, 5, 14, 30, 42, 43, 85, 86)}
     np.savez_compressed(os.path.join(HERE, "torch_linspace01.npz"), **lin)
+    only = sys.argv[1:]
     for name, cfg in CASES.items():
-        run_case(U, M, Rn, name, **cfg)
+        if not only or name in only:
+            run_case(U, M, Rn, name, **cfg)
 
 
 if __name__ == "__main__":

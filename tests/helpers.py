@@ -6,7 +6,7 @@ import numpy as np
 from ucnerf_b200 import synthetic
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = ("small_v3", "small_v5", "s126_v3", "moved_v3")
+CASES = ("small_v3", "small_v5", "s126_v3", "moved_v3", "s255_v5")
 
 
 def load_case(name):

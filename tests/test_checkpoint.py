@@ -62,6 +62,11 @@ def test_errors(tmp_path):
     torch.save({"something_else": {}}, p)
     with pytest.raises(L.UcnError):
         checkpoint.load_ckpt(p, m)
+    # a file without the encoder's weights does not load in the reference (strict): refused unless asked for
+    with pytest.raises(L.UcnError):
+        checkpoint.save_ckpt(str(tmp_path / "no_mvs.tar"), m)
+    p3 = checkpoint.save_ckpt(str(tmp_path / "no_mvs.tar"), m, allow_missing_mvs=True)
+    assert torch.load(p3, map_location="cpu", weights_only=True)[checkpoint.MVS_KEY] == {}
     # a 6-view checkpoint does not fit a 4-view model: same RuntimeError as the reference's strict load
     torch.save({checkpoint.FN_KEY: make_model(6).state_dict(), checkpoint.MVS_KEY: {}}, p)
     with pytest.raises(RuntimeError):

@@ -270,33 +270,60 @@ def test_philox_jitter_statistics_and_sortedness():
     assert 0.45 < u.mean().item() < 0.55 and 0.0 <= u.min().item() and u.max().item() <= 1.0 + 1e-4
 
 
-def test_config1_size_properties():
-    """BASELINE config-1 shapes (320x256, 3 views, 126 samples): oracle on a ray subset + size-independent
-    properties (row-tile sharding bit-identical to the whole frame)."""
-    from ucnerf_b200 import synthetic
+def _size_properties(H, W, V, S, seed, max_rays, shards):
+    """BASELINE-config shapes: the CUDA path at full size, checked by (a) the oracle on three 256-ray windows -- first
+    rows, the window that contains the dir-frame switch at ray 1024 (quirk Q4), last rows -- in fp32 (1e-4 rgb / depth)
+    and bf16 (1e-3 rgb), and (b) size-independent properties: the frame rendered as `shards` row tiles (what
+    `bench.py --gpus N` does, shard.row_tile) is bit-identical to the whole (launch-grouped) frame, z is sorted, depth
+    lies inside [near, far] of the widest stage."""
+    from ucnerf_b200 import shard, synthetic
     from ucnerf_b200.frame import FrameRenderer, PackedFrame, PackedWeights
-    H, W, V, S = 256, 320, 3, 126
-    sc = synthetic.make_scene(H, W, V, seed=11)
-    wts = synthetic.make_weights(V, seed=11)
+    sc = synthetic.make_scene(H, W, V, seed=seed)
+    wts = synthetic.make_weights(V, seed=seed)
     fr = PackedFrame.from_scene(sc, S, DEV, dir_switch=1024)
     pw = PackedWeights(wts, V, DEV)
-    t_rand = torch.rand((H * W, S), device=DEV, generator=torch.Generator(DEV).manual_seed(3))
-    for mode, tol in (("fp32", 1e-4), ("bf16", 1e-3)):
-        ren = FrameRenderer(fr, pw, mode, max_rays=H * W // 2)
-        rgb, depth = ren.render(t_rand=t_rand)
-        # sharded into 8 row tiles == whole frame, bit-identical
-        from ucnerf_b200 import shard
-        tiles = [ren.render(*shard.row_tile(H, W, p, 8), t_rand=t_rand[slice(*np.cumsum(shard.row_tile(H, W, p, 8)))])
-                 for p in range(8)]
-        assert torch.equal(torch.cat([t[0] for t in tiles]), rgb)
-        # oracle on three 256-ray windows (incl. the dir-frame switch at ray 1024)
-        osc, ow = O.OracleScene(sc, S, dir_switch=1024), O.OracleWeights(wts, V)
-        tr = t_rand.cpu().numpy()
-        for ray0 in (0, 900, H * W - 256):
-            rgb_o, depth_o = O.render_rays(osc, ow, ray0, 256, tr[ray0:ray0 + 256])
-            assert np.abs(rgb[ray0:ray0 + 256].cpu().numpy() - rgb_o).max() <= tol, mode
-            if mode == "fp32":
-                assert np.abs(depth[ray0:ray0 + 256].cpu().numpy() - depth_o).max() <= 1e-4
+    n = H * W
+    t_rand = torch.rand((n, S), device=DEV, generator=torch.Generator(DEV).manual_seed(3))
+    osc, ow = O.OracleScene(sc, S, dir_switch=1024), O.OracleWeights(wts, V)
+    windows = (0, 900, n - 256)
+    want = {r0: O.render_rays(osc, ow, r0, 256, t_rand[r0:r0 + 256].cpu().numpy()) for r0 in windows}
+    # bf16 (tcgen05): whole frame, launch-grouped
+    ren = FrameRenderer(fr, pw, "bf16", max_rays=max_rays)
+    rgb, depth = ren.render(t_rand=t_rand)
+    for r0 in windows:
+        err = np.abs(rgb[r0:r0 + 256].cpu().numpy() - want[r0][0]).max()
+        assert err <= 1e-3, ("bf16", r0, err)
+    assert bool(torch.isfinite(rgb).all()) and bool(torch.isfinite(depth).all())
+    assert 0.0 <= float(rgb.min()) and float(rgb.max()) <= 1.0
+    tiles = []
+    for p in range(shards):
+        r0, m = shard.row_tile(H, W, p, shards)
+        tiles.append(ren.render(r0, m, t_rand=t_rand[r0:r0 + m]))
+    assert torch.equal(torch.cat([t[0] for t in tiles]), rgb) and torch.equal(torch.cat([t[1] for t in tiles]), depth)
+    del tiles
+    # fp32: the windows only (ray0 / n_rays of the same frame), gate 1e-4 on rgb and depth
+    ren32 = FrameRenderer(fr, pw, "fp32", max_rays=256)
+    for r0 in windows:
+        r32, d32 = ren32.render(r0, 256, t_rand=t_rand[r0:r0 + 256])
+        assert np.abs(r32.cpu().numpy() - want[r0][0]).max() <= 1e-4, ("fp32 rgb", r0)
+        assert np.abs(d32.cpu().numpy() - want[r0][1]).max() <= 1e-4, ("fp32 depth", r0)
+
+
+def test_config1_size_properties():
+    """BASELINE config 1: 320x256, 3 source views, 126 samples."""
+    _size_properties(256, 320, 3, 126, seed=11, max_rays=256 * 320 // 2, shards=8)
+
+
+def test_config2_size_properties():
+    """BASELINE config 2 (the shape the headline number is quoted on): 640x512, 3 source views, 126 samples."""
+    _size_properties(512, 640, 3, 126, seed=12, max_rays=512 * 640 // 2, shards=8)
+
+
+def test_config5_size_properties():
+    """BASELINE config 5: 1280x1024, 5 source views, 255 samples (85-long stage sweeps, F = 85, two-pass img-feature
+    staging in K3, 8 scan groups in K4), launch-grouped like bench.py --workload c5."""
+    per_ray = 255 * (4 * (24 + 12 * 5 + 1) + 32)
+    _size_properties(1024, 1280, 5, 255, seed=13, max_rays=int(16e9 // per_ray) // 1280 * 1280, shards=8)
 
 
 @pytest.mark.parametrize("name", ("lin", "lin_jit", "disp_jit"))
@@ -379,3 +406,76 @@ def test_host_copy_cache_follows_the_tensor():
         u = torch.full((4, 4), float(k), device=DEV)
         assert frame._host(u).sum() == 16.0 * k
         del u
+
+
+def test_frame_cache_follows_tensor_identity():
+    """rays._FRAME_CACHE must never serve frame A's packed cameras / near-far maps to frame B: every frame of an eval
+    loop brings FRESH tensors (`_version` 0) that the caching allocator places at recycled addresses.  Render A, free
+    it, build a same-shaped B, and compare B with an uncached evaluation."""
+    from ucnerf_b200 import rays
+    ca, cb = load_case("small_v3"), load_case("moved_v3")
+    assert (ca["H"], ca["W"]) != (cb["H"], cb["W"])            # different goldens; B' below has A's shapes
+    from ucnerf_b200 import synthetic
+    scenes = [synthetic.make_scene(ca["H"], ca["W"], ca["V"], seed=100 + i, target_motion=0.5 * i) for i in range(4)]
+    S = ca["S"]
+    tr = T(ca["t_rand"])
+    outs, ptrs = [], set()
+    for sc in scenes:                                          # one frame at a time; previous tensors are freed
+        c = dict(ca, scene=sc)
+        outputs, pose_ref, _, _ = ref_inputs(c)
+        ptrs.add(outputs["stage1"]["depth_values"].data_ptr())
+        z = rays.build_rays_test(c["H"], c["W"], pose_ref["c2ws"][0], pose_ref["w2cs"][0], pose_ref["intrinsics"][0],
+                                 pose_ref["near_fars"], pose_ref["near_fars"][-1], S, outputs=outputs, t_rand=tr)[3]
+        outs.append(z.cpu().numpy())
+        del outputs, pose_ref, z
+    assert len(ptrs) < len(scenes)                             # the allocator did recycle addresses
+    for sc, got in zip(scenes, outs):
+        rays._FRAME_CACHE.clear()
+        py, px = O.chunk_pixels(ca["H"], ca["W"])
+        want = O.build_rays_test(O.OracleScene(sc, S), py, px, ca["t_rand"])["z"]
+        assert np.array_equal(bits(got), bits(want))
+    # same tensor objects again -> cache hit, same result; in-place edit -> miss (version bump)
+    c = dict(ca, scene=scenes[0])
+    outputs, pose_ref, _, _ = ref_inputs(c)
+    a = (c["H"], c["W"], pose_ref["c2ws"][0], pose_ref["w2cs"][0], pose_ref["intrinsics"][0], pose_ref["near_fars"],
+         pose_ref["near_fars"][-1], S)
+    n0 = len(rays._FRAME_CACHE)
+    z1 = rays.build_rays_test(*a, outputs=outputs, t_rand=tr)[3]
+    z2 = rays.build_rays_test(*a, outputs=outputs, t_rand=tr)[3]
+    assert torch.equal(z1, z2) and len(rays._FRAME_CACHE) == n0 + 1
+    outputs["stage3"]["depth_values"].mul_(1.01)
+    z3 = rays.build_rays_test(*a, outputs=outputs, t_rand=tr)[3]
+    assert not torch.equal(z1, z3)
+
+
+def test_default_seed_is_fresh_per_call():
+    """No t_rand, no seed: every call draws a new Philox key from torch's CPU generator (the reference draws a fresh
+    torch.rand per call, utils/utils.py:572,705); torch.manual_seed reproduces the sequence."""
+    from ucnerf_b200 import rays
+    from ucnerf_b200.frame import FrameRenderer, PackedFrame, PackedWeights
+    c = load_case("small_v3")
+    outputs, pose_ref, _, _ = ref_inputs(c)
+    a = (c["H"], c["W"], pose_ref["c2ws"][0], pose_ref["w2cs"][0], pose_ref["intrinsics"][0], pose_ref["near_fars"],
+         pose_ref["near_fars"][-1], c["S"])
+    torch.manual_seed(123)
+    z1 = rays.build_rays_test(*a, outputs=outputs)[3]
+    z2 = rays.build_rays_test(*a, outputs=outputs)[3]
+    torch.manual_seed(123)
+    z1b = rays.build_rays_test(*a, outputs=outputs)[3]
+    assert not torch.equal(z1, z2) and torch.equal(z1, z1b)
+    ren = FrameRenderer(PackedFrame.from_scene(c["scene"], c["S"], DEV), PackedWeights(c["weights"], c["V"], DEV), "fp32")
+    r1, r2 = ren.render()[0], ren.render()[0]
+    assert not torch.equal(r1, r2)
+    assert torch.equal(ren.render(seed=5)[0], ren.render(seed=5)[0])
+
+
+def test_wrong_device_tensor_is_rejected():
+    """Kernels launch on the current device's stream: a tensor of another device must raise, not fault."""
+    from ucnerf_b200 import lib as L
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    t = torch.zeros(4, device="cuda:1")
+    with pytest.raises(L.UcnError):
+        L.ptr(t)
+    with torch.cuda.device(1):
+        assert L.ptr(t).value == t.data_ptr()

@@ -39,10 +39,15 @@ def load_ckpt(path: str, network_fn: torch.nn.Module, network_mvs: Optional[torc
     return ckpt
 
 
-def save_ckpt(path: str, network_fn: torch.nn.Module, network_mvs=None) -> str:
-    """train.py:404-414.  ``network_mvs`` may be the encoder module, its state dict (e.g. the one ``load_ckpt``
-    returned) or None (an empty dict is written; the reference's loader then needs ``strict=False`` for the encoder)."""
+def save_ckpt(path: str, network_fn: torch.nn.Module, network_mvs=None, allow_missing_mvs: bool = False) -> str:
+    """train.py:404-414.  ``network_mvs`` is the encoder module or its state dict (e.g. the one ``load_ckpt``
+    returned).  The reference's loader calls ``EncodingNet.load_state_dict`` strictly (network/models.py:261-262), so a
+    file without the encoder's weights does NOT load there: passing None raises unless ``allow_missing_mvs=True`` (an
+    empty dict is then written, for renderer-only use with this package's ``load_ckpt``)."""
     d = os.path.dirname(os.path.abspath(path))
+    if network_mvs is None and not allow_missing_mvs:
+        raise L.UcnError("save_ckpt: network_mvs (encoder module or state dict) is required for a file the reference "
+                         "can load; pass allow_missing_mvs=True for a renderer-only checkpoint")
     os.makedirs(d, exist_ok=True)
     if network_mvs is None:
         mvs = {}

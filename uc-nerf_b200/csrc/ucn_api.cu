@@ -20,6 +20,17 @@ int ucn_cuda_status(cudaError_t e, const char *where) {
   return (int)e;
 }
 void ucn_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+int ucn_sm_count() {
+  static std::atomic<int> cache[kUcnMaxDevices];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kUcnMaxDevices) return 148;
+  int n = cache[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
 
 int ucn_mlp_forward_fp32(const ucn_weights *w, const float *ndc_pts, const float *feat, const float *angle, int R,
                          int S, float *raw, void *stream);

@@ -18,6 +18,22 @@
 int ucn_set_error(int code, const char *msg);
 int ucn_cuda_status(cudaError_t e, const char *where);
 void ucn_count_launch(int n = 1);
+int ucn_sm_count();            // multiprocessors of the CURRENT device (cached per device)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: `done` is the caller's static per-device
+// table of the byte counts already applied (one process may drive several GPUs).
+constexpr int kUcnMaxDevices = 64;
+template <typename Kernel>
+inline cudaError_t ucn_ensure_dyn_smem(Kernel k, int bytes, int (&done)[kUcnMaxDevices]) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kUcnMaxDevices) return cudaErrorInvalidDevice;
+  if (done[dev] >= bytes) return cudaSuccess;
+  e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) done[dev] = bytes;
+  return e;
+}
 
 #define UCN_LAUNCH_CHECK(where)                                    \
   do {                                                             \

@@ -190,11 +190,11 @@ static int launch_gather(bool from_z, const ucn_frame *f, const float *a, const 
   const size_t smem = tiled ? 0 : (size_t)kThreads * (F + 1) * sizeof(float);
   const unsigned blocks = (unsigned)((n + kThreads - 1) / kThreads);
   const cudaStream_t st = (cudaStream_t)stream;
-  static bool attr = false;
-  if (!attr) {
-    cudaFuncSetAttribute(gather_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    cudaFuncSetAttribute(gather_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    attr = true;
+  static int attr_a[kUcnMaxDevices], attr_b[kUcnMaxDevices];
+  if (!tiled) {
+    cudaError_t e = ucn_ensure_dyn_smem(gather_kernel<true, false>, 100 * 1024, attr_a);
+    if (e == cudaSuccess) e = ucn_ensure_dyn_smem(gather_kernel<false, false>, 100 * 1024, attr_b);
+    if (e != cudaSuccess) return ucn_cuda_status(e, "gather smem attribute");
   }
   if (from_z && tiled)
     gather_kernel<true, true><<<blocks, kThreads, 0, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);

@@ -142,7 +142,8 @@ depth_err_kernel(const float *__restrict__ gt, const float *__restrict__ pred, c
 
 inline unsigned grid_for(long long n) {
   const long long b = (n + kThreads - 1) / kThreads;
-  return (unsigned)(b < 148 * 8 ? (b < 1 ? 1 : b) : 148 * 8);      // persistent grid-stride: 8 CTAs per SM
+  const long long cap = 8ll * ucn_sm_count();                      // persistent grid-stride: 8 CTAs per SM
+  return (unsigned)(b < cap ? (b < 1 ? 1 : b) : cap);
 }
 
 }  // namespace

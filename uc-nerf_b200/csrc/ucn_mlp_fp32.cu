@@ -197,14 +197,12 @@ int ucn_mlp_forward_fp32(const ucn_weights *w, const float *ndc_pts, const float
   const int V = w->V, F = 24 + 12 * V + 1, LDF = (F + 3) & ~3;
   const int64_t N = (int64_t)R * S;
   const size_t smem = sizeof(Smem) + (size_t)TM * LDF * sizeof(float);
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  static int attr[kUcnMaxDevices];
+  {
+    cudaError_t e = ucn_ensure_dyn_smem(mlp_fp32_kernel, 200 * 1024, attr);
     if (e != cudaSuccess) return ucn_cuda_status(e, "mlp_fp32 smem attribute");
-    attr = true;
   }
-  int sms = 148;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+  const int sms = ucn_sm_count();
   const int64_t tiles = (N + TM - 1) / TM;
   const unsigned blocks = (unsigned)(tiles < sms ? tiles : sms);
   mlp_fp32_kernel<<<blocks, 256, smem, (cudaStream_t)stream>>>(w->f32, V, ndc_pts, feat, angle, N, S, raw);

@@ -414,15 +414,12 @@ int ucn_mlp_forward_tc(const ucn_weights *w, const float *ndc_pts, const float *
   UCN_CHECK_ARG(w->bf16, "ucn_mlp_forward: bf16 weight pack missing");
   UCN_CHECK_ARG(w->V <= 7, "ucn_mlp_forward: BF16_TC mode supports at most 7 source views");
   const long long N = (long long)R * S;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SmemLayout::total);
+  static int attr[kUcnMaxDevices];
+  {
+    cudaError_t e = ucn_ensure_dyn_smem(mlp_tc_kernel, (int)SmemLayout::total, attr);
     if (e != cudaSuccess) return ucn_cuda_status(e, "mlp_tc smem attribute");
-    attr = true;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = ucn_sm_count();
   const long long npairs = ((N + 127) / 128 + 1) / 2;
   const unsigned blocks = (unsigned)(npairs < sms ? npairs : sms);
   mlp_tc_kernel<<<blocks, kThreads, SmemLayout::total, (cudaStream_t)stream>>>(

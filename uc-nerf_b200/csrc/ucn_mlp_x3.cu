@@ -564,15 +564,12 @@ int ucn_mlp_forward_x3(const ucn_weights *w, const float *ndc_pts, const float *
   if (rc != 0) return ucn_set_error(UCN_E_ARG, "ucn_mlp_forward: cannot build the x3 schedule");
   const long long N = (long long)R * S;
   UCN_CHECK_ARG(N < (1ll << 31), "ucn_mlp_forward: more than 2^31 samples in one call; split the ray range");
-  static int attr_bytes = 0;
-  if (attr_bytes < (int)P.smem_total) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.smem_total);
+  static int attr[kUcnMaxDevices];
+  {
+    cudaError_t e = ucn_ensure_dyn_smem(mlp_x3_kernel, (int)P.smem_total, attr);
     if (e != cudaSuccess) return ucn_cuda_status(e, "mlp_x3 smem attribute");
-    attr_bytes = (int)P.smem_total;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = ucn_sm_count();
   const long long npairs = ((N + 127) / 128 + 1) / 2;
   const unsigned blocks = (unsigned)(npairs < sms ? npairs : sms);
   mlp_x3_kernel<<<blocks, kThreads, P.smem_total, (cudaStream_t)stream>>>(

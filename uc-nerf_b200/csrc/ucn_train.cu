@@ -719,11 +719,10 @@ int launch_gemm(const float *A, long long sai, long long sap, const float *B, lo
   dim3 grid(nblk(I, tile), nblk(J, tile), (unsigned)splits);
   UCN_CHECK_ARG(grid.y < 65536u, "ucn_linear: output too wide");
   if (tc) {
-    static bool attr = false;
-    if (!attr) {
-      cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM);
+    static int attr[kUcnMaxDevices];
+    {
+      cudaError_t e = ucn_ensure_dyn_smem(gemm_tc_kernel, (int)TC_SMEM, attr);
       if (e != cudaSuccess) return ucn_cuda_status(e, "gemm_tc smem attribute");
-      attr = true;
     }
     // float4 staging needs p contiguous, 16-byte aligned rows, and the last (partial) float4 of a row inside its pitch
     const long long P4 = (P + 3) & ~3ll;
@@ -738,9 +737,7 @@ int launch_gemm(const float *A, long long sai, long long sap, const float *B, lo
       UCN_LAUNCH_CHECK("split_b_kernel");
     }
     if (!(g_gemm_dbg & 32)) {
-      int dev = 0, sms = 148;
-      cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      const int sms = ucn_sm_count();
       const unsigned cap = (unsigned)(2 * sms) / grid.y / grid.z;             // two CTAs per SM are resident
       if (cap >= 1 && grid.x > cap) grid.x = cap;
     }
@@ -810,7 +807,7 @@ extern "C" int ucn_linear_bwd_weight(const float *dY, int64_t ldy, const float *
   const bool tc = g_gemm_mode == 0 && N >= 64 && K >= 16 && M >= 16;
   const int tile = tc ? 128 : BT;
   const long long tiles = (long long)((N + tile - 1) / tile) * ((K + tile - 1) / tile);
-  int splits = (int)((2 * 148 + tiles - 1) / tiles);
+  int splits = (int)((2 * ucn_sm_count() + tiles - 1) / tiles);
   const long long max_splits = (M + 255) / 256;
   if (splits > max_splits) splits = (int)max_splits;
   if (g_gemm_dbg >> 8) splits = g_gemm_dbg >> 8;      // timing switch (tools/ubench_gemm.py)

@@ -34,7 +34,10 @@ def _host_copy(x: torch.Tensor) -> np.ndarray:
     a = x.detach().to("cpu", torch.float32).contiguous().numpy()
     a.setflags(write=False)
     if len(_HOST_COPIES) >= 256:
-        _HOST_COPIES.clear()
+        for k in [k for k, v in _HOST_COPIES.items() if v[0]() is None]:     # dead tensors first ...
+            del _HOST_COPIES[k]
+        while len(_HOST_COPIES) >= 256:                                      # ... then the oldest entries, one by one
+            _HOST_COPIES.pop(next(iter(_HOST_COPIES)))
     _HOST_COPIES[key] = (weakref.ref(base), x._version, a)
     return a
 
@@ -57,6 +60,13 @@ def _dev(x, device) -> torch.Tensor:
     if isinstance(x, np.ndarray):
         x = torch.from_numpy(np.ascontiguousarray(x))
     return x.detach().to(device=device, dtype=torch.float32).contiguous()
+
+
+def fresh_seed() -> int:
+    """A new 63-bit Philox key from torch's CPU generator (so torch.manual_seed controls the sequence): the default of
+    every sampling entry point when the caller gives neither `t_rand` nor `seed`, mirroring the reference's fresh
+    torch.rand per call (utils/utils.py:572,705)."""
+    return int(torch.randint(0, 2 ** 62, (1,), device="cpu").item())
 
 
 _T_VALS: Dict = {}
@@ -253,10 +263,15 @@ class FrameRenderer:
         self.ws_bytes = int(self.lib.ucn_frame_workspace_bytes(C.byref(frame.c), self.max_rays, self.mode))
         self.ws = torch.empty(self.ws_bytes, device=frame.device, dtype=torch.uint8)
 
-    def render(self, ray0: int = 0, n_rays: Optional[int] = None, t_rand: Optional[torch.Tensor] = None, seed: int = 0,
-               out_rgb: Optional[torch.Tensor] = None, out_depth: Optional[torch.Tensor] = None,
+    def render(self, ray0: int = 0, n_rays: Optional[int] = None, t_rand: Optional[torch.Tensor] = None,
+               seed: Optional[int] = None, out_rgb: Optional[torch.Tensor] = None, out_depth: Optional[torch.Tensor] = None,
                timers: Optional[dict] = None):
+        """`t_rand` [n, S] injects the jitter; otherwise the in-kernel Philox stream keyed by (`seed`, global ray id,
+        sample) is used -- `seed=None` draws a fresh seed per call (frame.fresh_seed)."""
         f = self.frame
+        if t_rand is None and seed is None:
+            seed = fresh_seed()
+        seed = int(seed or 0)
         total = f.c.H * f.c.W
         n = total - ray0 if n_rays is None else int(n_rays)
         rgb = out_rgb if out_rgb is not None else torch.empty((n, 3), device=f.device, dtype=torch.float32)
@@ -309,7 +324,7 @@ class FrameRenderer:
                                                              None, None, st), "K4"))
 
 
-def render_frame(frame: PackedFrame, weights: PackedWeights, mode: str = "bf16", t_rand=None, seed: int = 0,
+def render_frame(frame: PackedFrame, weights: PackedWeights, mode: str = "bf16", t_rand=None, seed: Optional[int] = None,
                  ray0: int = 0, n_rays: Optional[int] = None, max_rays: Optional[int] = None):
     """One call per target view: (rgb [R,3], depth [R]) for rays ray0..ray0+R of the row-major pixel grid."""
     return FrameRenderer(frame, weights, mode, max_rays).render(ray0, n_rays, t_rand, seed)
@@ -363,7 +378,7 @@ class HostSweep:
             self.copied[slot].record(self.copy_stream)
         self.pending[slot] = tag
 
-    def submit(self, i: int, host_maps, next_host_maps=None, seed: int = 0):
+    def submit(self, i: int, host_maps, next_host_maps=None, seed: Optional[int] = None):
         """Enqueue view i (host->device copy if not prefetched, K0 packing, K1..K4, device->host copy of the image) and
         return without synchronising; `result(i)` waits for it.  Submitting view i+1 before collecting view i keeps the
         GPU busy while the host builds the next frame (at most two views in flight: two staging sets, two images)."""
@@ -391,7 +406,7 @@ class HostSweep:
         self.done[i & 1].synchronize()
         return self.out_host[i & 1]
 
-    def render(self, i: int, host_maps, next_host_maps=None, seed: int = 0):
+    def render(self, i: int, host_maps, next_host_maps=None, seed: Optional[int] = None):
         """submit + result: one view, synchronous (the reference's eval loop syncs per chunk, train.py:274-275)."""
         self.submit(i, host_maps, next_host_maps, seed)
         return self.result(i)

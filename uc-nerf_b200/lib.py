@@ -132,15 +132,24 @@ def check(rc: int, what: str = ""):
         raise UcnError(f"{what or 'libucnerf'} failed (code {rc}): {msg}")
 
 
+_PEER_RANGES = []          # [(lo, hi)] address ranges of peer-mapped buffers (shard.PeerFrameBuffer)
+
+
 def ptr(t):
-    """Device pointer of a contiguous fp32/int32 CUDA tensor (or None)."""
+    """Device pointer of a contiguous fp32/int32 CUDA tensor (or None).  The tensor must live on the CURRENT device
+    (the kernels launch on its stream and use its attributes) unless it is a registered peer mapping."""
     if t is None:
         return None
     if not t.is_cuda:
         raise UcnError("libucnerf has no CPU path: tensor must live on a CUDA device")
     if not t.is_contiguous():
         raise UcnError("tensor must be contiguous")
-    return C.c_void_p(t.data_ptr())
+    import torch
+    a = t.data_ptr()
+    if t.device.index != torch.cuda.current_device() and not any(lo <= a < hi for lo, hi in _PEER_RANGES):
+        raise UcnError(f"tensor lives on {t.device} but the current device is cuda:{torch.cuda.current_device()}: "
+                       "wrap the call in `with torch.cuda.device(t.device)`")
+    return C.c_void_p(a)
 
 
 def stream_ptr():

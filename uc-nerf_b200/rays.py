@@ -20,21 +20,62 @@ import torch
 
 from . import lib as L
 from . import train_path as _tp
-from .frame import PackedFrame, _host, host_scalar, linspace01
+import weakref
 
-_FRAME_CACHE: Dict[tuple, PackedFrame] = {}
+from .frame import PackedFrame, _host, fresh_seed, host_scalar, linspace01
+
+# key -> (weak references to the base tensors of the key, PackedFrame).  A PackedFrame holds cameras by value and its own
+# packed copies of the maps, so nothing keeps the caller's tensors alive: the key is therefore the IDENTITY of each
+# tensor object (id of its base + view geometry + `_version`), and a hit additionally requires every weak reference to
+# be alive and to be that very object -- a later frame whose fresh tensors land on recycled addresses (or recycled
+# ids) can never hit an earlier frame's entry.
+_FRAME_CACHE: Dict[tuple, tuple] = {}
 _CACHE_MAX = 8
 
 
 def _key(*tensors):
-    return tuple((t.data_ptr(), t._version, tuple(t.shape)) if isinstance(t, torch.Tensor) else t for t in tensors)
+    key, bases = [], []
+    for t in tensors:
+        if isinstance(t, torch.Tensor):
+            base = t._base if t._base is not None else t
+            key.append((id(base), t._version, t.storage_offset(), tuple(t.shape), tuple(t.stride()), t.dtype))
+            bases.append(base)
+        else:
+            key.append(t)
+    return tuple(key), bases
 
 
-def _cache_put(key, val):
+def _cache_get(key, bases):
+    hit = _FRAME_CACHE.get(key)
+    if hit is None:
+        return None
+    refs, val = hit
+    if len(refs) == len(bases) and all(r() is b for r, b in zip(refs, bases)):
+        return val
+    del _FRAME_CACHE[key]                # an id was recycled by a new tensor object: stale entry
+    return None
+
+
+def _cache_put(key, bases, val):
+    for k in [k for k, (refs, _) in _FRAME_CACHE.items() if any(r() is None for r in refs)]:
+        del _FRAME_CACHE[k]              # entries whose tensors are gone can never hit again
     if len(_FRAME_CACHE) >= _CACHE_MAX:
         _FRAME_CACHE.pop(next(iter(_FRAME_CACHE)))
-    _FRAME_CACHE[key] = val
+    _FRAME_CACHE[key] = ([weakref.ref(b) for b in bases], val)
     return val
+
+
+_INV_SCALE: Dict[tuple, torch.Tensor] = {}
+
+
+def _inv_scale(W: int, H: int, device) -> torch.Tensor:
+    """torch.tensor([W-1, H-1]).to(device) of the reference (utils/utils.py:585,726), cached per (W, H, device): the
+    pageable host->device copy behind it synchronises the stream once per call otherwise.  Read-only by contract."""
+    key = (int(W), int(H), str(device))
+    t = _INV_SCALE.get(key)
+    if t is None:
+        t = _INV_SCALE[key] = torch.tensor([W - 1, H - 1]).to(device)
+    return t
 
 
 def _need_cuda(t: torch.Tensor, what: str):
@@ -50,24 +91,27 @@ def sample_points_uniform(device, near, far, num_samples, num_rays):
 
 def _rays_frame(H, W, S, tgt_to_world, world_to_ref, intrinsic, near, far, outputs) -> PackedFrame:
     dvs = [outputs[s]["depth_values"] for s in ("stage1", "stage2", "stage3")]
-    key = ("rays", H, W, S, host_scalar(near), host_scalar(far)) + _key(tgt_to_world, world_to_ref, intrinsic, *dvs)
-    fr = _FRAME_CACHE.get(key)
+    tkey, bases = _key(tgt_to_world, world_to_ref, intrinsic, *dvs)
+    key = ("rays", H, W, S, host_scalar(near), host_scalar(far)) + tkey
+    fr = _cache_get(key, bases)
     if fr is None:
         fr = PackedFrame(tgt_to_world.device)
         fr.set_target(H, W, S, intrinsic, tgt_to_world, world_to_ref, near, far)
         fr.pack_depth_values(dvs)
-        _cache_put(key, fr)
+        _cache_put(key, bases, fr)
     return fr
 
 
 def build_rays_test(H, W, tgt_to_world, world_to_ref, intrinsic, near_fars_ref, near_fars, N_samples, pad=0,
                     ref_idx=0, use_cpu=False, chunk=-1, idx=-1, outputs=None, t_rand: Optional[torch.Tensor] = None,
-                    seed: int = 0):
+                    seed: Optional[int] = None):
     """utils/utils.py:600-739.  Returns (ray_coordinate_world [R,S,3], ray_dir_world [R,3],
     ray_coordinate_ref {stage1,stage2,stage3,ndc: [R,S,3]}, depth_candidates [R,S], rays_os [R,3], ndc_parameters).
 
     ``t_rand`` ([R,S] uniforms) is the one extension: the reference draws ``torch.rand`` internally
-    (:705); pass it to reproduce a given draw, omit it for the in-kernel Philox stream keyed by ``seed``."""
+    (:705); pass it to reproduce a given draw, omit it for the in-kernel Philox stream keyed by ``seed``.  With
+    neither, a fresh 64-bit seed is drawn from torch's CPU generator on every call -- like the reference, two calls
+    never reuse a jitter pattern, and ``torch.manual_seed`` makes the sequence reproducible."""
     if use_cpu:
         raise L.UcnError("build_rays_test(use_cpu=True): no CPU path in this implementation")
     _need_cuda(tgt_to_world, "build_rays_test")
@@ -85,11 +129,13 @@ def build_rays_test(H, W, tgt_to_world, world_to_ref, intrinsic, near_fars_ref, 
     if t_rand is not None:
         t_rand = t_rand.to(device=device, dtype=torch.float32).contiguous()
         assert tuple(t_rand.shape) == (R, S)
-    L.check(L.load().ucn_raygen_sample(C.byref(fr.c), None, lo, R, L.ptr(fr.t_vals), L.ptr(t_rand), int(seed),
+    elif seed is None:
+        seed = fresh_seed()
+    L.check(L.load().ucn_raygen_sample(C.byref(fr.c), None, lo, R, L.ptr(fr.t_vals), L.ptr(t_rand), int(seed or 0),
                                        L.ptr(z), L.ptr(rays_d), L.ptr(pts), L.ptr(ndc), L.stream_ptr()),
             "ucn_raygen_sample")
     rays_o = tgt_to_world[:3, -1].clone().reshape(1, 3).expand(R, -1)
-    inv_scale = torch.tensor([W - 1, H - 1]).to(device)
+    inv_scale = _inv_scale(W, H, device)
     ndc_parameters = {"w2c_ref": world_to_ref, "intrinsic_ref": intrinsic, "inv_scale": inv_scale, "near": near,
                       "far": far, "pad": pad}
     rays_ndc = {"stage1": ndc[0], "stage2": ndc[1], "stage3": ndc[2], "ndc": ndc[3]}
@@ -187,8 +233,9 @@ def _maps_frame(volume_feature, imgs, img_feat, confidence, pose_ref) -> PackedF
     vols = None if volume_feature is None else [volume_feature[s]["volume_feature_no_ref"]
                                                 for s in ("stage1", "stage2", "stage3")]
     cams = () if pose_ref is None else (pose_ref["w2cs"], pose_ref["intrinsics"])
-    key = ("maps",) + _key(imgs, img_feat, confidence, *cams, *(vols or ()))
-    fr = _FRAME_CACHE.get(key)
+    tkey, bases = _key(imgs, img_feat, confidence, *cams, *(vols or ()))
+    key = ("maps",) + tkey
+    fr = _cache_get(key, bases)
     if fr is None:
         ref = imgs if imgs is not None else confidence
         fr = PackedFrame(ref.device)
@@ -208,7 +255,7 @@ def _maps_frame(volume_feature, imgs, img_feat, confidence, pose_ref) -> PackedF
             conf = confidence.to(torch.float32).reshape(H, W).contiguous()
             fr._keep["conf"] = conf
             fr.c.conf = conf.data_ptr()
-        _cache_put(key, fr)
+        _cache_put(key, bases, fr)
     return fr
 
 
@@ -254,7 +301,8 @@ def build_color_volume(point_samples, pose_ref, imgs, near_far=None, img_feat=No
 
 # ---- training sampler -------------------------------------------------------------------
 
-def select_training_pixels(H, W, confidence, coords, N_rays, patch_num, patch_size, generator=None):
+def select_training_pixels(H, W, confidence, coords, N_rays, patch_num, patch_size, generator=None,
+                           is_precrop_iters=False):
     """Ray SELECTION of build_rays (utils/utils.py:450-479,169-215,217-247,274-320), kept in PyTorch as the survey
     prescribes: patch_num/2 patches drawn by confidence-multinomial, patch_num/2 by (1 - confidence), uniform random
     pixels up to N_rays, then the sparse-depth coordinates.  The reference's per-patch Python loop is replaced by one
@@ -276,8 +324,12 @@ def select_training_pixels(H, W, confidence, coords, N_rays, patch_num, patch_si
         cols = (pj * ps + sj)[:, None, None] + grid[None, None, :]            # [half, 1, ps]
         pix.append(torch.stack((rows.expand(-1, ps, ps).reshape(-1), cols.expand(-1, ps, ps).reshape(-1))))
     n_rand = N_rays - 2 * half * ps * ps
-    xs = torch.randint(0, W, (n_rand,), device=device, generator=generator)
-    ys = torch.randint(0, H, (n_rand,), device=device, generator=generator)
+    if is_precrop_iters and float(torch.rand((1,))) > 0.3:                   # centre crop, utils/utils.py:241-246
+        xs = torch.randint(W // 6, W - W // 6, (n_rand,), device=device, generator=generator)
+        ys = torch.randint(H // 6, H - H // 6, (n_rand,), device=device, generator=generator)
+    else:
+        xs = torch.randint(0, W, (n_rand,), device=device, generator=generator)
+        ys = torch.randint(0, H, (n_rand,), device=device, generator=generator)
     pix.append(torch.stack((ys, xs)))
     if coords is not None:
         pix.append(coords.to(device).t().long())                              # coords [N,2] = (row, col)
@@ -286,7 +338,8 @@ def select_training_pixels(H, W, confidence, coords, N_rays, patch_num, patch_si
 
 def build_rays(args, imgs, mvs_confidence, sparse_depths, coords, pose_ref, w2cs, c2ws, intrinsics, N_rays, N_samples,
                pad=0, is_precrop_iters=False, ref_idx=0, with_depth=False, outputs=None,
-               pixel_coordinates: Optional[torch.Tensor] = None, t_rand: Optional[torch.Tensor] = None, seed: int = 0):
+               pixel_coordinates: Optional[torch.Tensor] = None, t_rand: Optional[torch.Tensor] = None,
+               seed: Optional[int] = None):
     """utils/utils.py:400-597 (training sampler).  Returns the reference's 9-tuple
     (ray_coordinate_world [R,S,3], ray_dir_world [R,3], colors [R,3], points_all {stage1,stage2,stage3,ndc},
     depth_candidates [R,S], rays_os [R,3], rays_depths (None), ndc_parameters, pixel_coordinates_int [2,R]).
@@ -294,7 +347,9 @@ def build_rays(args, imgs, mvs_confidence, sparse_depths, coords, pose_ref, w2cs
     Selection stays in PyTorch (`select_training_pixels`); everything after it -- ray directions, per-pixel stage
     near/far, 3 x S/3 sweeps, sort, jitter, world points, the four NDC tensors -- is K1's explicit-pixel mode, the
     same arithmetic as `build_rays_test`.  Extensions: `pixel_coordinates` injects a selection (parity tests),
-    `t_rand` injects the jitter the reference draws with torch.rand (:572)."""
+    `t_rand` injects the jitter the reference draws with torch.rand (:572); without `t_rand` the in-kernel Philox stream
+    is keyed by `seed`, and with neither a fresh seed is drawn per call from torch's CPU generator (every training step
+    resamples its depths, as the reference does)."""
     if not with_depth:
         raise L.UcnError("build_rays(with_depth=False) is dead in the reference (depth_candidate undefined, "
                          "utils/utils.py:575); train.py:147 always passes with_depth=True")
@@ -303,7 +358,8 @@ def build_rays(args, imgs, mvs_confidence, sparse_depths, coords, pose_ref, w2cs
     N, V, C3, H, W = imgs.shape
     S = int(N_samples)
     if pixel_coordinates is None:
-        pixel_coordinates = select_training_pixels(H, W, mvs_confidence, coords, N_rays, args.patch_num, args.patch_size)
+        pixel_coordinates = select_training_pixels(H, W, mvs_confidence, coords, N_rays, args.patch_num, args.patch_size,
+                                                   is_precrop_iters=is_precrop_iters)
     pix = pixel_coordinates.to(device=device, dtype=torch.float32).contiguous()
     R = pix.shape[1]
     w2c_ref, intrinsic_ref = pose_ref['w2cs'][ref_idx], pose_ref['intrinsics'][ref_idx]
@@ -316,13 +372,15 @@ def build_rays(args, imgs, mvs_confidence, sparse_depths, coords, pose_ref, w2cs
     if t_rand is not None:
         t_rand = t_rand.to(device=device, dtype=torch.float32).contiguous()
         assert tuple(t_rand.shape) == (R, S)
-    L.check(L.load().ucn_raygen_sample(C.byref(fr.c), L.ptr(pix), 0, R, L.ptr(fr.t_vals), L.ptr(t_rand), int(seed),
+    elif seed is None:
+        seed = fresh_seed()
+    L.check(L.load().ucn_raygen_sample(C.byref(fr.c), L.ptr(pix), 0, R, L.ptr(fr.t_vals), L.ptr(t_rand), int(seed or 0),
                                        L.ptr(z), L.ptr(rays_d), L.ptr(pts), L.ptr(ndc), L.stream_ptr()),
             "ucn_raygen_sample")
     pix_int = pix.long()
     colors = imgs[0, 0][:, pix_int[0], pix_int[1]].permute(1, 0)              # :497-501, target view = index 0
     rays_o = c2ws[0][:3, -1].clone().reshape(1, 3).expand(R, -1)
     ndc_parameters = {"w2c_ref": w2c_ref, "intrinsic_ref": intrinsic_ref,
-                      "inv_scale": torch.tensor([W - 1, H - 1]).to(device), "near": near, "far": far, "pad": pad}
+                      "inv_scale": _inv_scale(W, H, device), "near": near, "far": far, "pad": pad}
     points_all = {"stage1": ndc[0], "stage2": ndc[1], "stage3": ndc[2], "ndc": ndc[3]}
     return pts, rays_d, colors, points_all, z, rays_o, None, ndc_parameters, pix_int

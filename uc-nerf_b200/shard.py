@@ -92,6 +92,7 @@ class PeerFrameBuffer:
             dist.broadcast_object_list(payload, src=root, group=group)
             if not self.is_root:
                 L.check(self.lib.ucn_peer_open(payload[0], C.byref(self._base)), "ucn_peer_open")
+            L._PEER_RANGES.append((self._base.value, self._base.value + 16 * n))
             # [n][3] rgb followed by [n] depth inside the one allocation
             # (no device= here: torch must alias the mapping, never copy it to the local GPU)
             self.rgb = torch.as_tensor(_DeviceBlob(self._base.value, (n, 3), self))
@@ -106,6 +107,10 @@ class PeerFrameBuffer:
             torch.cuda.synchronize()
             dist.barrier(group=self.group)
             self.rgb = self.depth = None
+            from . import lib as L
+            rng = (self._base.value, self._base.value + 16 * self.H * self.W)
+            if rng in L._PEER_RANGES:
+                L._PEER_RANGES.remove(rng)
             if not self.is_root:
                 self.lib.ucn_peer_close(self._base)
             dist.barrier(group=self.group)
