@@ -90,27 +90,25 @@ def run_reference(args):
 
 
 def run(args, ClockSampler, peaks):
+    """`bench.py --workload c4`: one JSON line for the training step."""
+    import torch.distributed as dist
+    import bench
+    ctx = bench.init_dist()
+    line = measure(args, ClockSampler, peaks, ctx, full=True)
+    if line is not None:
+        print(json.dumps(line))
+    if ctx[1] > 1:
+        dist.destroy_process_group()
+
+
+def measure(args, ClockSampler, peaks, ctx, full=True):
+    """The config-4 measurement on the current process group; returns the line (rank 0) or None."""
     import torch
     import torch.distributed as dist
     from types import SimpleNamespace
     from ucnerf_b200 import lib as L, losses, models, rays, renderer, synthetic, train_path as TP
 
-    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        # NCCL prints its version banner on fd 1 when the communicator is created: stdout carries the JSON line only
-        saved_fd = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=dev)
-            dist.barrier()
-            torch.cuda.synchronize()
-        finally:
-            sys.stdout.flush()
-            os.dup2(saved_fd, 1)
-            os.close(saved_fd)
+    rank, world, local, dev = ctx
     L.check(L.load().ucn_check_device(), "ucn_check_device")
     H, W, V, S = CFG["H"], CFG["W"], CFG["V"], CFG["S"]
     N_rays, n_depth = CFG["batch_size"], CFG["n_depth"]
@@ -208,17 +206,18 @@ def run(args, ClockSampler, peaks):
     for i in range(max(3, args.warmup)):
         step(i, read_loss=True)
     loss0 = box["loss"]
-    sampler = ClockSampler(local)
-    if rank == 0:
+    sampler = ClockSampler(local) if full else None
+    if rank == 0 and sampler:
         sampler.start()
     timers = []
     L.launch_count(reset=True)
     ms, wall_ms = timed(lambda i: step(100 + i, timers), args.steps)
     launches = L.launch_count() // args.steps
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop() if (rank == 0 and sampler) else None
     e2e_ms, e2e_wall = timed(lambda i: step(200 + i, None, read_loss=True), args.steps)
     e2e_ms = max(e2e_ms, e2e_wall)
     kern = {p: sum(ev[k].elapsed_time(ev[k + 1]) for ev in timers) / args.steps for k, p in enumerate(phases)}
+    line = None
     if rank == 0:
         pk = peaks()
         n_samples = R * S
@@ -233,7 +232,11 @@ def run(args, ClockSampler, peaks):
                        "arithmetic": "fp32 operands split into three bf16 parts, six tcgen05 MMAs per product, fp32 accumulate (fp32-class: gradients within 1e-4 of the reference's autograd); heads and elementwise in fp32",
                        "loss": "5*img2mse + 0.05*(weighted sparse-depth MSE + patch smoothness) + 0.008*scale-invariant patch gradient (train.py:164-188 minus the encoder-side cas_mvsnet_loss)",
                        "l2": "saved activations 2.7 GB per step exceed the 126 MB L2",
-                       "parallelism": f"data parallel x{world}: one all-reduce of {n_grad_params} fp32 gradients per step"},
+                       "parallelism": f"data parallel x{world}: one all-reduce of {n_grad_params} fp32 gradients "
+                                      f"({n_grad_params * 4 / 1e6:.2f} MB) per step -- the renderer MLP's parameters; the CasMVSNet "
+                                      "encoder the reference also trains (934 304 parameters, network/models.py:249-250, "
+                                      "train.py:136) is outside this path, so the map gradients K2b produces end at leaf tensors "
+                                      "and are not in the bucket"},
             "e2e": {"value": world * R / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": n_depth * 16,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
             "gpu_launches": launches, "clocks": clocks,
@@ -246,12 +249,10 @@ def run(args, ClockSampler, peaks):
             "kernels_ms_per_step": kern, "wall_ms_per_step": wall_ms,
             "loss_first_last": [loss0, box["loss"]],
         }
-        if world == 1 and not args.no_cpu_baseline:
+        if full and world == 1 and not args.no_cpu_baseline:
             n = args.cpu_rays or 256
             cpu_step_rate(min(n, 64))
             rate, dt, cores = cpu_step_rate(n)
             line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
                                     "sample": f"{n} of the 2048 rays of one training step, forward + backward ({dt:.1f} s)"}
-        print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    return line

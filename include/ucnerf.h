@@ -115,6 +115,16 @@ int ucn_pack_channels_last(const float *src, float *dst, int B, int Cn, int64_t 
 int ucn_pack_volume(const float *src, float *dst, int D, int h, int w, void *stream);
 /* depth_values [D][h][w] -> [h][w][2] = (plane 0, plane D-1)   (utils/utils.py:668-683) */
 int ucn_pack_nearfar(const float *depth_values, float *dst, int D, int h, int w, void *stream);
+/* Row-band variants for ray-tile sharding: the volumes live in the TARGET frustum
+ * (train.py:235 world_to_ref = pose_ref['w2cs'][0] is the target's own camera), so the rays of image rows [r0, r1)
+ * touch only stage rows [r0/ds - 1, r1/ds + 1].  These pack source rows [row0, row0 + rows) of planes that hold h rows
+ * each into a dense band; the caller stores `band - row0 * row_bytes` in ucn_frame.vol / .nearfar so that the
+ * kernels keep indexing absolute rows (ucn_frame.h stays the FULL height: border clamping is unchanged). */
+int ucn_pack_volume_rows(const float *src, float *dst, int D, int h, int w, int row0, int rows, void *stream);
+int ucn_pack_nearfar_rows(const float *depth_values, float *dst, int D, int h, int w, int row0, int rows, void *stream);
+/* host -> device copy of rows [row0, row0+rows) of `planes` fp32 [h][w] planes into a dense [planes][rows][w] band
+ * (one strided DMA; src_host should be pinned).  The per-rank share of the per-pose map upload of a sharded sweep. */
+int ucn_h2d_rows(float *dst, const float *src_host, int64_t planes, int h, int w, int row0, int rows, void *stream);
 size_t ucn_weights_f32_bytes(int V);
 size_t ucn_weights_bf16_bytes(int V);
 size_t ucn_weights_bf16x3_bytes(int V);

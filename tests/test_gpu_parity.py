@@ -479,3 +479,48 @@ def test_wrong_device_tensor_is_rejected():
         L.ptr(t)
     with torch.cuda.device(1):
         assert L.ptr(t).value == t.data_ptr()
+
+
+def test_row_band_frame_matches_whole_frame():
+    """Ray-tile sharding packs / uploads only the row band of the target-frustum maps a tile touches
+    (PackedFrame.set_row_band, HostSweep band_keys -> ucn_h2d_rows + ucn_pack_*_rows).  Every tile of a banded
+    frame must be bit-identical to the same rays of the whole frame, from resident maps and from host maps."""
+    from ucnerf_b200 import lib as L, shard, synthetic
+    from ucnerf_b200.frame import FrameRenderer, HostSweep, PackedFrame, PackedWeights
+    H, W, V, S = 48, 40, 3, 126
+    sc = synthetic.make_scene(H, W, V, seed=40, target_motion=0.5)
+    pw = PackedWeights(synthetic.make_weights(V, seed=40), V, DEV)
+    whole = FrameRenderer(PackedFrame.from_scene(sc, S, DEV, dir_switch=1024), pw, "bf16").render(seed=9)
+    host = {"dv": [torch.from_numpy(a).pin_memory() for a in sc.depth_values],
+            "vol": [torch.from_numpy(a).pin_memory() for a in sc.volumes],
+            "feat": torch.from_numpy(sc.img_feats).pin_memory(), "imgs": torch.from_numpy(sc.imgs).pin_memory(),
+            "conf": torch.from_numpy(sc.confidence).pin_memory()}
+    resident = {k: ([t.to(DEV) for t in v] if isinstance(v, list) else v.to(DEV)) for k, v in host.items()}
+    for world in (3, 4):
+        for rank in range(world):
+            ray0, n = shard.row_tile(H, W, rank, world)
+            rows = (ray0 // W, (ray0 + n) // W)
+
+            def make_frame(maps):
+                fr = PackedFrame(DEV)
+                fr.set_target(H, W, S, sc.K[0], sc.c2ws[0], sc.w2cs[0], sc.near_fars[0, 0], sc.near_fars[0, 1],
+                              dir_rot0=sc.w2cs[0], dir_rot1=sc.w2cs[1], dir_switch=1024)
+                fr.set_sources(sc.w2cs[1:], sc.K[1:])
+                fr.set_row_band(*rows)
+                return fr.pack_depth_values(maps["dv"]).pack_volumes(maps["vol"]).pack_sources(maps["imgs"], maps["feat"], maps["conf"])
+            fr = make_frame(resident)                                   # full maps in HBM, band packed
+            assert fr.map_bytes < PackedFrame.from_scene(sc, S, DEV).map_bytes
+            rgb, depth = FrameRenderer(fr, pw, "bf16", max_rays=n).render(ray0, n, seed=9)
+            assert torch.equal(rgb, whole[0][ray0:ray0 + n]) and torch.equal(depth, whole[1][ray0:ray0 + n]), (world, rank)
+            with pytest.raises(L.UcnError):                             # rays outside the band are refused
+                FrameRenderer(fr, pw, "bf16", max_rays=n).render(0, H * W, seed=9)
+            sweep = HostSweep(pw, make_frame, n, "bf16", DEV, ray0=ray0, frame_hw=(H, W), band_keys=("dv", "vol", "conf"))
+            full_bytes = sum(t.numel() * 4 for _, _, t in HostSweep._walk(host))
+            assert sweep.h2d_bytes(host) < full_bytes
+            out = sweep.render(0, host, None, seed=9)
+            assert torch.equal(out[:, :3], whole[0][ray0:ray0 + n].cpu()) and torch.equal(out[:, 3], whole[1][ray0:ray0 + n].cpu())
+    # a target that is NOT the reference camera cannot be banded
+    fr = PackedFrame(DEV)
+    fr.set_target(H, W, S, sc.K[0], sc.c2ws[0], sc.w2cs[1], sc.near_fars[0, 0], sc.near_fars[0, 1])
+    with pytest.raises(L.UcnError):
+        fr.set_row_band(0, 8)

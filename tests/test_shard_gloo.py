@@ -63,3 +63,30 @@ def test_sharded_render_matches_single_rank(tmp_path):
     rgb, depth = O.render_rays(osc, ow, 0, H * W, c["t_rand"])
     assert np.array_equal(got["rgb"], rgb) and np.array_equal(got["depth"], depth)
     assert np.abs(rgb - c["g"]["rgb"]).max() <= 1e-4
+
+
+def test_stage_band_covers_every_row_a_tile_touches():
+    """frame.stage_band: rows of a stage map that the rays of image rows [r0, r1) read through
+    grid_sample(align_corners=False, border) when the volume is pixel-aligned with the target view
+    (utils/utils.py:852-857; ATen GridSampler.h unnormalize: ((g+1)*h - 1)/2 with g = 2*y/(H-1) - 1)."""
+    import numpy as np
+    from ucnerf_b200.frame import stage_band
+    from ucnerf_b200.shard import row_tile
+    for H, W in ((512, 640), (1024, 1280), (256, 320), (16, 20), (8, 12)):
+        for world in (1, 2, 3, 4, 8):
+            for rank in range(world):
+                ray0, n = row_tile(H, W, rank, world)
+                if n == 0:
+                    continue
+                r0, r1 = ray0 // W, (ray0 + n) // W
+                for ds in (4, 2, 1):
+                    h = H // ds
+                    a, b = stage_band(H, r0, r1, ds)
+                    assert 0 <= a < b <= h
+                    y = np.arange(r0, r1, dtype=np.float64)
+                    for jitter in (-1e-3, 0.0, 1e-3):                 # projection round-off moves the row by << 1e-3
+                        x = np.clip((y + jitter) / (H - 1) * h - 0.5, 0, h - 1)
+                        lo, hi = np.floor(x).astype(int), np.minimum(np.floor(x).astype(int) + 1, h - 1)
+                        assert lo.min() >= a and hi.max() < b, (H, world, rank, ds, a, b, lo.min(), hi.max())
+                    # near/far lookup of K1: pixel row // ds (utils/utils.py:660-683)
+                    assert r0 // ds >= a and (r1 - 1) // ds < b

@@ -41,23 +41,25 @@ __global__ void pack_cl_kernel(const float *__restrict__ src, float *__restrict_
 // per column instead of D planes h*w*32 bytes apart.  Block = one image row y x 16 columns x, staged through shared
 // memory so that both the NCDHW reads (along x) and the packed writes (16*D*8 contiguous floats) are coalesced.
 constexpr int kVolTileX = 16;
-__global__ void pack_volume_kernel(const float *__restrict__ src, float *__restrict__ dst, int D, int h, int w) {
+// (row band: block row y of the OUTPUT is source row y + row0; h is the source's row count)
+__global__ void pack_volume_kernel(const float *__restrict__ src, float *__restrict__ dst, int D, int h, int w, int row0) {
   extern __shared__ float tile[];                       // [kVolTileX][D*8 + 1]
   const int y = blockIdx.y, x0 = blockIdx.x * kVolTileX, ld = D * 8 + 1;
   const int nx = min(kVolTileX, w - x0);
   for (int idx = threadIdx.x; idx < 8 * D * kVolTileX; idx += blockDim.x) {
     const int x = idx % kVolTileX, z = (idx / kVolTileX) % D, c = idx / (kVolTileX * D);
-    if (x < nx) tile[x * ld + z * 8 + c] = src[(((size_t)c * D + z) * h + y) * w + x0 + x];
+    if (x < nx) tile[x * ld + z * 8 + c] = src[(((size_t)c * D + z) * h + y + row0) * w + x0 + x];
   }
   __syncthreads();
   float *out = dst + ((size_t)y * w + x0) * D * 8;
   for (int e = threadIdx.x; e < nx * D * 8; e += blockDim.x) out[e] = tile[(e / (D * 8)) * ld + e % (D * 8)];
 }
 
-__global__ void pack_nearfar_kernel(const float *__restrict__ dv, float *__restrict__ dst, int D, int hw) {
+// (row band: n texels starting at texel `first` of planes that hold hw texels each)
+__global__ void pack_nearfar_kernel(const float *__restrict__ dv, float *__restrict__ dst, int D, int hw, int first, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= hw) return;
-  reinterpret_cast<float2 *>(dst)[i] = make_float2(dv[i], dv[(size_t)(D - 1) * hw + i]);
+  if (i >= n) return;
+  reinterpret_cast<float2 *>(dst)[i] = make_float2(dv[first + i], dv[(size_t)(D - 1) * hw + first + i]);
 }
 
 // dst_f32[(row(k))*ldn + n_off + n] = src[n*K + k]; row(k) = (k >= shift_from ? k+1 : k) + k_off
@@ -113,24 +115,49 @@ extern "C" int ucn_pack_channels_last(const float *src, float *dst, int B, int C
   return UCN_OK;
 }
 
-extern "C" int ucn_pack_volume(const float *src, float *dst, int D, int h, int w, void *stream) {
-  UCN_CHECK_ARG(src && dst && D > 0 && D <= 256 && h > 0 && w > 0, "ucn_pack_volume: bad argument");
-  const dim3 grid((w + kVolTileX - 1) / kVolTileX, h);
+extern "C" int ucn_pack_volume_rows(const float *src, float *dst, int D, int h, int w, int row0, int rows, void *stream) {
+  UCN_CHECK_ARG(src && dst && D > 0 && D <= 256 && h > 0 && w > 0 && row0 >= 0 && rows >= 0 && row0 + rows <= h,
+                "ucn_pack_volume: bad argument");
+  if (rows == 0) return UCN_OK;
+  const dim3 grid((w + kVolTileX - 1) / kVolTileX, rows);
   const size_t smem = (size_t)kVolTileX * (D * 8 + 1) * sizeof(float);
+  static int attr[kUcnMaxDevices];
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(pack_volume_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = ucn_ensure_dyn_smem(pack_volume_kernel, (int)smem, attr);
     if (e != cudaSuccess) return ucn_cuda_status(e, "pack_volume smem attribute");
   }
-  pack_volume_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(src, dst, D, h, w);
+  pack_volume_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(src, dst, D, h, w, row0);
   UCN_LAUNCH_CHECK("pack_volume_kernel");
   return UCN_OK;
 }
+extern "C" int ucn_pack_volume(const float *src, float *dst, int D, int h, int w, void *stream) {
+  return ucn_pack_volume_rows(src, dst, D, h, w, 0, h, stream);
+}
 
-extern "C" int ucn_pack_nearfar(const float *depth_values, float *dst, int D, int h, int w, void *stream) {
-  UCN_CHECK_ARG(depth_values && dst && D > 0 && h > 0 && w > 0, "ucn_pack_nearfar: bad argument");
-  pack_nearfar_kernel<<<(h * w + 255) / 256, 256, 0, (cudaStream_t)stream>>>(depth_values, dst, D, h * w);
+extern "C" int ucn_pack_nearfar_rows(const float *depth_values, float *dst, int D, int h, int w, int row0, int rows,
+                                     void *stream) {
+  UCN_CHECK_ARG(depth_values && dst && D > 0 && h > 0 && w > 0 && row0 >= 0 && rows >= 0 && row0 + rows <= h,
+                "ucn_pack_nearfar: bad argument");
+  if (rows == 0) return UCN_OK;
+  const int n = rows * w;
+  pack_nearfar_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(depth_values, dst, D, h * w, row0 * w, n);
   UCN_LAUNCH_CHECK("pack_nearfar_kernel");
   return UCN_OK;
+}
+extern "C" int ucn_pack_nearfar(const float *depth_values, float *dst, int D, int h, int w, void *stream) {
+  return ucn_pack_nearfar_rows(depth_values, dst, D, h, w, 0, h, stream);
+}
+
+// Host -> device copy of a row band of `planes` row-major [h][w] fp32 planes (one strided DMA: cudaMemcpy2DAsync with
+// one "row" per plane).  src is the HOST tensor (pinned for an asynchronous copy), dst the dense [planes][rows][w] band.
+extern "C" int ucn_h2d_rows(float *dst, const float *src_host, int64_t planes, int h, int w, int row0, int rows, void *stream) {
+  UCN_CHECK_ARG(dst && src_host && planes > 0 && h > 0 && w > 0 && row0 >= 0 && rows >= 0 && row0 + rows <= h,
+                "ucn_h2d_rows: bad argument");
+  if (rows == 0) return UCN_OK;
+  const size_t width = (size_t)rows * w * sizeof(float);
+  cudaError_t e = cudaMemcpy2DAsync(dst, width, src_host + (size_t)row0 * w, (size_t)h * w * sizeof(float), width,
+                                    (size_t)planes, cudaMemcpyHostToDevice, (cudaStream_t)stream);
+  return e == cudaSuccess ? UCN_OK : ucn_cuda_status(e, "ucn_h2d_rows: cudaMemcpy2DAsync");
 }
 
 extern "C" size_t ucn_weights_f32_bytes(int V) { return ucn::F32Layout(V).total * sizeof(float); }

@@ -86,8 +86,27 @@ def linspace01(n: int, device) -> torch.Tensor:
     return t
 
 
+STAGE_DOWN = (4, 2, 1)          # stage k maps live at H/4, H/2, H (network/mvs_models.py:649)
+
+
+def stage_band(H: int, r0: int, r1: int, ds: int, halo: int = 2):
+    """Rows [a, b) of a stage map (H/ds rows) that the rays of image rows [r0, r1) can touch.  The volumes live in the
+    target's own frustum (train.py:235: world_to_ref is the target camera), so a sample of pixel row y projects back to
+    row y: grid_sample(align_corners=False) reads stage rows floor(y*h/(H-1) - 0.5) and +1, i.e. within one row of
+    y/ds; `halo` = 2 leaves a spare row on each side."""
+    h = H // ds
+    return max(0, r0 // ds - halo), min(h, -(-r1 // ds) + halo)
+
+
 class PackedFrame:
-    """Cameras (by value) + packed maps (device) for one target view == one ``ucn_frame``."""
+    """Cameras (by value) + packed maps (device) for one target view == one ``ucn_frame``.
+
+    Row-band mode (`set_row_band`, ray-tile sharding): only the rows of the target-frustum maps (depth hypotheses,
+    volumes, confidence) that the rays of image rows [r0, r1) touch are packed -- from full maps or from maps that
+    were already cut to the band (e.g. by a banded host->device copy, HostSweep).  The frame keeps the FULL map
+    heights (border clamping is unchanged) and stores band pointers shifted back by the band's first row, so the
+    kernels index absolute rows.  Source images / features are always whole: projections into the source views are
+    not row-local."""
 
     def __init__(self, device):
         self.device = torch.device(device)
@@ -97,6 +116,31 @@ class PackedFrame:
         self.c = L.Frame()
         self._keep: Dict[str, torch.Tensor] = {}
         self._t_vals: Optional[torch.Tensor] = None
+        self.band = None                       # (r0, r1) image rows this frame can render, None = all
+        self._halo = 2
+
+    def set_row_band(self, r0: int, r1: int, halo: int = 2):
+        """Restrict the frame to image rows [r0, r1) (call after set_target, before pack_*)."""
+        c = self.c
+        if not (0 <= r0 < r1 <= c.H):
+            raise L.UcnError(f"row band [{r0}, {r1}) outside the {c.H}-row image")
+        m = np.array(c.c2w[:], np.float64).reshape(4, 4) @ np.array(c.w2c[:], np.float64).reshape(4, 4)
+        if np.abs(m - np.eye(4)).max() > 1e-4:
+            raise L.UcnError("row bands need world_to_ref to be the target's own camera (inverse of tgt_to_world), as in "
+                             "the reference's eval loop (train.py:235,247): the volumes are then pixel-aligned with the rays")
+        self.band, self._halo = (int(r0), int(r1)), int(halo)
+        return self
+
+    def _rows(self, k_ds: int, full_h: int, src_h: int):
+        """(source row offset, first band row a, band rows) for a stage map given with src_h rows."""
+        if self.band is None:
+            return 0, 0, src_h
+        a, b = stage_band(self.c.H, self.band[0], self.band[1], k_ds, self._halo)
+        if src_h == full_h:
+            return a, a, b - a
+        if src_h == b - a:
+            return 0, a, b - a
+        raise L.UcnError(f"stage map has {src_h} rows: expected the full {full_h} or the band's {b - a}")
 
     # ---- cameras ----------------------------------------------------------------------------
     def set_target(self, H, W, S, intrinsic, c2w, w2c, near, far, dir_rot0=None, dir_rot1=None, dir_switch=None):
@@ -144,10 +188,12 @@ class PackedFrame:
             dv = _dev(dv, self.device)
             dv = dv[0] if dv.dim() == 4 else dv
             D, h, w = dv.shape
-            self.c.D[k], self.c.h[k], self.c.w[k] = D, h, w
-            dst = self._alloc(f"nearfar{k}", h, w, 2)
-            L.check(lib.ucn_pack_nearfar(L.ptr(dv.contiguous()), L.ptr(dst), D, h, w, st), "ucn_pack_nearfar")
-            self.c.nearfar[k] = dst.data_ptr()
+            full_h = h if self.band is None else self.c.H // STAGE_DOWN[k]
+            src0, a, rows = self._rows(STAGE_DOWN[k], full_h, h)
+            self.c.D[k], self.c.h[k], self.c.w[k] = D, full_h, w
+            dst = self._alloc(f"nearfar{k}", rows, w, 2)
+            L.check(lib.ucn_pack_nearfar_rows(L.ptr(dv.contiguous()), L.ptr(dst), D, h, w, src0, rows, st), "ucn_pack_nearfar")
+            self.c.nearfar[k] = dst.data_ptr() - a * w * 2 * 4
         return self
 
     def pack_volumes(self, volumes: Sequence):
@@ -159,12 +205,14 @@ class PackedFrame:
             Cn, D, h, w = vol.shape
             if Cn != 8:
                 raise L.UcnError("feature volumes must have 8 channels")
-            if self.c.D[k] and (self.c.D[k], self.c.h[k], self.c.w[k]) != (D, h, w):
+            full_h = h if self.band is None else self.c.H // STAGE_DOWN[k]
+            if self.c.D[k] and (self.c.D[k], self.c.h[k], self.c.w[k]) != (D, full_h, w):
                 raise L.UcnError("volume / depth_values shape mismatch")
-            self.c.D[k], self.c.h[k], self.c.w[k] = D, h, w
-            dst = self._alloc(f"vol{k}", h, w, D, 8)
-            L.check(lib.ucn_pack_volume(L.ptr(vol.contiguous()), L.ptr(dst), D, h, w, st), "ucn_pack_volume")
-            self.c.vol[k] = dst.data_ptr()
+            src0, a, rows = self._rows(STAGE_DOWN[k], full_h, h)
+            self.c.D[k], self.c.h[k], self.c.w[k] = D, full_h, w
+            dst = self._alloc(f"vol{k}", rows, w, D, 8)
+            L.check(lib.ucn_pack_volume_rows(L.ptr(vol.contiguous()), L.ptr(dst), D, h, w, src0, rows, st), "ucn_pack_volume")
+            self.c.vol[k] = dst.data_ptr() - a * w * D * 8 * 4
         return self
 
     def pack_sources(self, imgs, img_feat, confidence):
@@ -174,13 +222,17 @@ class PackedFrame:
         imgs = imgs[0] if imgs.dim() == 5 else imgs
         V, C3, H, W = imgs.shape
         feat = _dev(img_feat, self.device).reshape(V, 8, H, W)
-        conf = _dev(confidence, self.device).reshape(H, W)
+        conf = _dev(confidence, self.device)
+        conf = conf.reshape(conf.shape[-2], W)
+        _, conf_a, _ = self._rows(1, H, conf.shape[0])          # whole map, or already cut to the band's rows
+        if conf.shape[0] == H:
+            conf_a = 0
         rgb = self._alloc("rgb", V, H, W, 4)
         ft = self._alloc("feat", V, H, W, 8)
         L.check(lib.ucn_pack_channels_last(L.ptr(imgs.contiguous()), L.ptr(rgb), V, C3, H * W, 4, st), "pack rgb")
         L.check(lib.ucn_pack_channels_last(L.ptr(feat), L.ptr(ft), V, 8, H * W, 8, st), "pack feat")
         self._keep["conf"] = conf
-        self.c.rgb, self.c.feat, self.c.conf = rgb.data_ptr(), ft.data_ptr(), conf.data_ptr()
+        self.c.rgb, self.c.feat, self.c.conf = rgb.data_ptr(), ft.data_ptr(), conf.data_ptr() - conf_a * W * 4
         return self
 
     @property
@@ -274,6 +326,8 @@ class FrameRenderer:
         seed = int(seed or 0)
         total = f.c.H * f.c.W
         n = total - ray0 if n_rays is None else int(n_rays)
+        if f.band is not None and n > 0 and not (f.band[0] * f.c.W <= ray0 and ray0 + n <= f.band[1] * f.c.W):
+            raise L.UcnError(f"rays [{ray0}, {ray0 + n}) leave the frame's row band {f.band}")
         rgb = out_rgb if out_rgb is not None else torch.empty((n, 3), device=f.device, dtype=torch.float32)
         depth = out_depth if out_depth is not None else torch.empty((n,), device=f.device, dtype=torch.float32)
         for lo in range(0, n, self.max_rays):
@@ -338,12 +392,21 @@ class HostSweep:
     (two staging sets), so the PCIe transfer of every view is inside the sweep but off its critical path; the
     result is copied device->host and the call synchronises, as the reference's eval loop does per chunk
     (train.py:274-275).  `make_frame(dev_maps)` builds the PackedFrame (cameras + ucn_pack_* of the staged maps).
-    """
+
+    Ray-tile sharding (one process per GPU): `ray0` / `n_rays` select this rank's row tile.  With
+    `band_keys`, the host->device copy of those map groups (the target-frustum maps: depth hypotheses, volumes,
+    confidence) carries only the rows the tile can touch (`stage_band`, one strided DMA per map: ucn_h2d_rows) --
+    `make_frame` then receives band-shaped tensors and must call `PackedFrame.set_row_band` before packing.  With
+    `peer` (two shard.PeerFrameBuffer, double buffered), K4 stores the tile straight into the root's frame buffer
+    over NVLink; one 4-byte all-reduce per view is the barrier, after which the root copies the whole frame
+    (16 B / ray) to its pinned host buffer.  `result(i)` returns that buffer on the root ([3n | n] floats, see
+    `split_frame`) and None elsewhere."""
 
     def __init__(self, weights: PackedWeights, make_frame, n_rays: int, mode: str = "bf16", device="cuda",
-                 max_rays: Optional[int] = None):
+                 max_rays: Optional[int] = None, ray0: int = 0, frame_hw=None, band_keys=(), peer=None, group=None):
         self.device = torch.device(device)
         self.weights, self.make_frame, self.mode, self.n_rays = weights, make_frame, mode, int(n_rays)
+        self.ray0, self.peer, self.group = int(ray0), peer, group
         self.max_rays = int(max_rays or n_rays)         # rays per launch group (bounds the workspace)
         self.copy_stream = torch.cuda.Stream(device=self.device)
         self.staging = [None, None]
@@ -351,10 +414,24 @@ class HostSweep:
         self.free = [torch.cuda.Event(), torch.cuda.Event()]
         self.pending = [None, None]                     # id of the host map set staged (or in flight) per slot
         self.renderer: Optional[FrameRenderer] = None
-        self.rgb = torch.empty((self.n_rays, 3), device=self.device)
-        self.depth = torch.empty((self.n_rays,), device=self.device)
-        self.out_dev = [torch.empty((self.n_rays, 4), device=self.device) for _ in range(2)]
-        self.out_host = [torch.empty((self.n_rays, 4), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.band_keys, self.rows = tuple(band_keys), None
+        if self.band_keys:
+            H, W = frame_hw
+            if self.ray0 % W or self.n_rays % W:
+                raise L.UcnError("banded copies need a tile of whole image rows")
+            self.frame_hw, self.rows = (int(H), int(W)), (self.ray0 // W, (self.ray0 + self.n_rays) // W)
+        if peer is None:
+            self.rgb = torch.empty((self.n_rays, 3), device=self.device)
+            self.depth = torch.empty((self.n_rays,), device=self.device)
+            self.out_dev = [torch.empty((self.n_rays, 4), device=self.device) for _ in range(2)]
+            self.out_host = [torch.empty((self.n_rays, 4), dtype=torch.float32).pin_memory() for _ in range(2)]
+        else:
+            import torch.distributed as dist
+            self._dist = dist
+            self.is_root = peer[0].is_root
+            self.flag = torch.zeros(1, device=self.device)
+            total = peer[0].H * peer[0].W
+            self.out_host = [torch.empty((4 * total,), dtype=torch.float32).pin_memory() for _ in range(2)] if self.is_root else None
         self.done = [torch.cuda.Event(), torch.cuda.Event()]
         self._frames = [None, None]
         for e in self.free:
@@ -366,17 +443,51 @@ class HostSweep:
             for j, t in enumerate(v if isinstance(v, (list, tuple)) else [v]):
                 yield k, j, t
 
+    def _band_of(self, t):
+        """(first row, rows) of the band of host map `t` ([..., h, w], h = H/ds) for this rank's tile."""
+        H = self.frame_hw[0]
+        h = t.shape[-2]
+        if H % h:
+            raise L.UcnError(f"map with {h} rows is not a stage map of a {H}-row frame")
+        a, b = stage_band(H, self.rows[0], self.rows[1], H // h)
+        return a, b - a
+
+    def _staging_like(self, k, t):
+        if k in self.band_keys:
+            shape = list(t.shape)
+            shape[-2] = self._band_of(t)[1]
+            return torch.empty(shape, device=self.device)
+        return torch.empty(t.shape, device=self.device)
+
     def _enqueue(self, slot, host_maps, tag):
         if self.staging[slot] is None:
-            self.staging[slot] = {k: ([torch.empty(t.shape, device=self.device) for t in v] if isinstance(v, (list, tuple))
-                                      else torch.empty(v.shape, device=self.device)) for k, v in host_maps.items()}
+            self.staging[slot] = {k: ([self._staging_like(k, t) for t in v] if isinstance(v, (list, tuple))
+                                      else self._staging_like(k, v)) for k, v in host_maps.items()}
+        lib = L.load()
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self.free[slot])            # the previous user of this staging set is done
+            st = C.c_void_p(self.copy_stream.cuda_stream)
             for k, j, t in self._walk(host_maps):
                 dst = self.staging[slot][k]
-                (dst[j] if isinstance(dst, list) else dst).copy_(t, non_blocking=True)
+                dst = dst[j] if isinstance(dst, list) else dst
+                if k in self.band_keys:
+                    a, rows = self._band_of(t)
+                    h, w = t.shape[-2:]
+                    if t.is_cuda or not t.is_contiguous() or t.dtype != torch.float32:
+                        raise L.UcnError("banded copies take contiguous fp32 HOST maps")
+                    L.check(lib.ucn_h2d_rows(L.ptr(dst), C.c_void_p(t.data_ptr()), t.numel() // (h * w), h, w, a, rows, st),
+                            "ucn_h2d_rows")
+                else:
+                    dst.copy_(t, non_blocking=True)
             self.copied[slot].record(self.copy_stream)
         self.pending[slot] = tag
+
+    def h2d_bytes(self, host_maps) -> int:
+        """Bytes one `_enqueue` moves over PCIe for `host_maps` (banded groups count their band only)."""
+        n = 0
+        for k, _, t in self._walk(host_maps):
+            n += (t.numel() // t.shape[-2] * self._band_of(t)[1] if k in self.band_keys else t.numel()) * 4
+        return n
 
     def submit(self, i: int, host_maps, next_host_maps=None, seed: Optional[int] = None):
         """Enqueue view i (host->device copy if not prefetched, K0 packing, K1..K4, device->host copy of the image) and
@@ -394,17 +505,37 @@ class HostSweep:
             self.renderer = FrameRenderer(fr, self.weights, self.mode, max_rays=self.max_rays)
         self.renderer.frame = fr
         self._frames[slot] = fr                                     # keeps the packed maps alive until the view is collected
-        self.renderer.render(seed=seed, out_rgb=self.rgb, out_depth=self.depth)
-        self.free[slot].record(main)
-        torch.cat((self.rgb, self.depth[:, None]), dim=1, out=self.out_dev[slot])
-        self.out_host[slot].copy_(self.out_dev[slot], non_blocking=True)
+        if self.peer is None:
+            self.renderer.render(self.ray0, self.n_rays, seed=seed, out_rgb=self.rgb, out_depth=self.depth)
+            self.free[slot].record(main)
+            torch.cat((self.rgb, self.depth[:, None]), dim=1, out=self.out_dev[slot])
+            self.out_host[slot].copy_(self.out_dev[slot], non_blocking=True)
+        else:
+            buf = self.peer[slot]
+            out_rgb, out_depth = buf.tile(self.ray0, self.n_rays)   # K4's stores land in the root's HBM
+            self.renderer.render(self.ray0, self.n_rays, seed=seed, out_rgb=out_rgb, out_depth=out_depth)
+            self.free[slot].record(main)
+            # stream-ordered barrier: completes once every rank's tile of view i is stored.  It also orders the root's
+            # read-out of view i-1 (earlier in the root's stream) before any rank's stores of view i+1 into that buffer.
+            self._dist.all_reduce(self.flag, group=self.group)
+            if self.is_root:
+                self.out_host[slot].copy_(buf.raw, non_blocking=True)
         self.done[slot].record(main)
         self.pending[slot] = None
 
     def result(self, i: int) -> torch.Tensor:
-        """Pinned host image [n_rays, 4] = (rgb, depth) of view i (valid until view i+2 is submitted)."""
+        """Pinned host image of view i (valid until view i+2 is submitted): [n_rays, 4] = (rgb, depth); in peer mode the
+        root's whole frame as [3n | n] floats (`split_frame`), None on the other ranks."""
         self.done[i & 1].synchronize()
+        if self.peer is not None and not self.is_root:
+            return None
         return self.out_host[i & 1]
+
+    @staticmethod
+    def split_frame(flat: torch.Tensor):
+        """[3n | n] -> (rgb [n,3], depth [n]) views of a peer-mode result."""
+        n = flat.numel() // 4
+        return flat[:3 * n].view(n, 3), flat[3 * n:]
 
     def render(self, i: int, host_maps, next_host_maps=None, seed: Optional[int] = None):
         """submit + result: one view, synchronous (the reference's eval loop syncs per chunk, train.py:274-275)."""

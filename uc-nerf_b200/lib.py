@@ -53,6 +53,9 @@ _SIGS = {
     "ucn_pack_channels_last": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int64, C.c_int, _fp]),
     "ucn_pack_volume": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp]),
     "ucn_pack_nearfar": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp]),
+    "ucn_pack_volume_rows": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _fp]),
+    "ucn_pack_nearfar_rows": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _fp]),
+    "ucn_h2d_rows": (C.c_int, [_fp, _fp, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _fp]),
     "ucn_weights_f32_bytes": (C.c_size_t, [C.c_int]),
     "ucn_weights_bf16_bytes": (C.c_size_t, [C.c_int]),
     "ucn_weights_bf16x3_bytes": (C.c_size_t, [C.c_int]),

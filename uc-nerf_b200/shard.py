@@ -97,6 +97,7 @@ class PeerFrameBuffer:
             # (no device= here: torch must alias the mapping, never copy it to the local GPU)
             self.rgb = torch.as_tensor(_DeviceBlob(self._base.value, (n, 3), self))
             self.depth = torch.as_tensor(_DeviceBlob(self._base.value + 12 * n, (n,), self))
+            self.raw = torch.as_tensor(_DeviceBlob(self._base.value, (4 * n,), self))      # [3n | n], one copy for the read-out
             if self.rgb.data_ptr() != self._base.value or self.depth.data_ptr() != self._base.value + 12 * n:
                 raise RuntimeError("PeerFrameBuffer: torch copied the peer mapping instead of aliasing it")
         dist.barrier(group=group)
@@ -106,7 +107,7 @@ class PeerFrameBuffer:
         if self._base:
             torch.cuda.synchronize()
             dist.barrier(group=self.group)
-            self.rgb = self.depth = None
+            self.rgb = self.depth = self.raw = None
             from . import lib as L
             rng = (self._base.value, self._base.value + 16 * self.H * self.W)
             if rng in L._PEER_RANGES:
