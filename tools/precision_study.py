@@ -28,10 +28,19 @@ def pe(x, L):
     return np.concatenate(out, -1).astype(np.float32)
 
 
-def mlp(sd, V, ndc, feat, angle, qa, qw, qh=None):
-    """qa/qw: mantissa bits of activation/weight operands; qh: bits for the tiny head layers"""
+GROUPS = {"pts_bias_depth_fine": "film", "pts_bias_confidence": "fb", "feature_linear": "feat",
+          "views_linears.0": "vv", "view_confi_linears.0": "vv"}
+
+
+def mlp(sd, V, ndc, feat, angle, qa, qw, qh=None, per_group=None):
+    """qa/qw: mantissa bits of activation/weight operands; qh: bits for the tiny head layers;
+    per_group: {"film"|"trunk"|"fb"|"feat"|"vv": (qa, qw)} overrides per layer group (K3's MMA rounds)"""
     qh = qh or (qa, qw)
-    def lin(name, x, a=qa, w=qw):
+    per_group = per_group or {}
+    def lin(name, x, a=None, w=None):
+        grp = GROUPS.get(name, "trunk" if name.startswith("pts_linears") else None)
+        ga, gw = per_group.get(grp, (qa, qw))
+        a, w = (ga if a is None else a), (gw if w is None else w)
         Wm, b = sd[f"nerf.{name}.weight"], sd[f"nerf.{name}.bias"]
         return (rnd(x, a).astype(np.float64) @ rnd(Wm, w).astype(np.float64).T + b).astype(np.float32)
     N = ndc.shape[0]
@@ -84,6 +93,18 @@ def main():
             rgb, dep = O.raw2outputs(raw.reshape(R, S, 4), o["z"])
             e = np.abs(rgb - g["rgb"])
             print(f"  {label:32s} rgb max {e.max():.2e} mean {e.mean():.2e} p99 {np.quantile(e, .99):.2e}  raw max {np.abs(raw-ref_raw).max():.2e}")
+        # per-layer-group table: everything split-bf16 (15/15 = three MMA passes) except ONE group (or the whole tail)
+        # at a cheaper operand format.  Heads stay fp32 (CUDA cores in K3).  passes: (7,7)/(10,10) = 1, (15,7)/(10,21) = 2
+        fmts = (("bf16 1-pass", (7, 7)), ("fp16 1-pass", (10, 10)), ("bf16x2 A, bf16 W (2)", (15, 7)),
+                ("bf16 A, bf16x2 W (2)", (7, 15)), ("fp16 A, fp16x2 W (2)", (10, 21)))
+        print("  -- one group (or the tail fb+feat+vv) cheaper, rest split-bf16; heads fp32 --")
+        for grp in ("film", "trunk", "fb", "feat", "vv", "tail"):
+            for label, q in fmts:
+                pg = {g_: q for g_ in (("fb", "feat", "vv") if grp == "tail" else (grp,))}
+                raw = mlp(c["weights"], V, ndc, F, angs, 15, 15, (23, 23), pg)
+                rgb, dep = O.raw2outputs(raw.reshape(R, S, 4), o["z"])
+                e = np.abs(rgb - g["rgb"])
+                print(f"  {grp:6s} {label:24s} rgb max {e.max():.2e} p99 {np.quantile(e, .99):.2e}  raw max {np.abs(raw-ref_raw).max():.2e}")
 
 
 if __name__ == "__main__":

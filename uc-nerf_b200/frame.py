@@ -463,6 +463,9 @@ class HostSweep:
         if self.staging[slot] is None:
             self.staging[slot] = {k: ([self._staging_like(k, t) for t in v] if isinstance(v, (list, tuple))
                                       else self._staging_like(k, v)) for k, v in host_maps.items()}
+            # the caching allocator may hand out blocks whose previous owner still has kernels in flight on the main
+            # stream (safe for main-stream users only): the copy stream's first write must come after them
+            self.copy_stream.wait_stream(torch.cuda.current_stream(self.device))
         lib = L.load()
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self.free[slot])            # the previous user of this staging set is done

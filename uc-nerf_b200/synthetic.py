@@ -116,7 +116,7 @@ def make_scene(H: int, W: int, V: int = 3, seed: int = 0, target_motion: float =
             lo = np.clip(ck - half, near * 0.5, None)
             hi = np.clip(ck + half, None, far * 1.5)
         t = np.linspace(0.0, 1.0, D)[:, None, None]
-        depth_values.append((lo[None] * (1 - t) + hi[None] * t)[None].astype(np.float32))
+        depth_values.append(np.ascontiguousarray((lo[None] * (1 - t) + hi[None] * t)[None].astype(np.float32)))
     volumes, img_feats, imgs, conf = [], None, None, None
     if maps:
         for D, ds in zip(STAGE_DEPTHS, STAGE_DOWN):
