@@ -5,7 +5,9 @@ import numpy as np, torch
 from ucnerf_b200 import lib as L, synthetic
 from ucnerf_b200.frame import PackedWeights
 lib = L.load()
-lib.ucn_debug_set_trace.argtypes = [C.c_void_p]
+V1 = os.environ.get("UCN_X3_KERNEL", "2") == "1"
+set_trace = lib.ucn_debug_set_trace if V1 else lib.ucn_debug_set_trace_p      # round-1 kernel / pipelined kernel
+set_trace.argtypes = [C.c_void_p]
 V, S, R = 3, 126, 148 * 2 * 128 * 6 // 126
 F = 24 + 12 * V + 1
 pw = PackedWeights(synthetic.make_weights(V, seed=0), V, "cuda")
@@ -22,14 +24,14 @@ buf = torch.zeros(7 * CAP * 2, dtype=torch.int64, device="cuda")
 def run():
     L.check(lib.ucn_mlp_forward_tiles(C.byref(pw.c), L.ptr(ndc), L.ptr(feat), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
 flags = int(os.environ.get("X3_DBG", "0"))
-L.check(lib.ucn_debug_set_flags(flags), "flags")
+L.check((lib.ucn_debug_set_flags if V1 else lib.ucn_debug_set_flags_p)(flags), "flags")
 run(); torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record(); run(); e1.record(); torch.cuda.synchronize()
 print(f"flags {flags}: kernel {e0.elapsed_time(e1):.3f} ms for {R * S} samples -> {R * S / e0.elapsed_time(e1) / 1e3:.1f} Msamples/s")
-L.check(lib.ucn_debug_set_trace(C.c_void_p(buf.data_ptr())), "trace")
+L.check(set_trace(C.c_void_p(buf.data_ptr())), "trace")
 run(); torch.cuda.synchronize()
-L.check(lib.ucn_debug_set_trace(None), "trace")
+L.check(set_trace(None), "trace")
 b = buf.cpu().numpy().reshape(7, CAP, 2)
 ev = []
 for who in range(7):
@@ -39,6 +41,6 @@ ev.sort(); t0 = ev[0][0]
 names = {1: "mma_start", 2: "mma_issued", 3: "epi_wake", 4: "epi_done", 5: "blk_issued", 6: "point"}
 lo, hi = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (0, 200)
 for t, tag, r, who, pay in ev[lo:hi]:
-    extra = f"  wfull_wait={pay}" if tag == 2 else ""
+    extra = (f"  wfull_wait={pay & 0xFFFFF} go_wait={pay >> 20}" if not V1 else f"  wfull_wait={pay}") if tag == 2 else ""
     print(f"{t - t0:>8} {names[tag]:<11} r{r} {'wg' if tag in (3, 4, 6) else 'slot'}{who}{extra}")
 print("events", len(ev), "span cycles", ev[-1][0] - t0)

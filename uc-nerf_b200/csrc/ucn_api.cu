@@ -5,6 +5,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <stdlib.h>
 
 #include "ucn_common.cuh"
 
@@ -39,6 +40,27 @@ int ucn_mlp_forward_tc(const ucn_weights *w, const float *ndc_pts, const float *
 int ucn_mlp_forward_x3(const ucn_weights *w, const float *ndc_pts, const float *feat, long long f_tile_stride,
                        long long f_k_stride, long long f_row_stride, const float *angle, int R, int S, float *raw,
                        void *stream);
+int ucn_mlp_forward_x3p(const ucn_weights *w, const float *ndc_pts, const float *feat, long long f_tile_stride,
+                       long long f_k_stride, long long f_row_stride, const float *angle, int R, int S, float *raw,
+                       void *stream);
+// Which split-bf16 kernel serves UCN_MLP_BF16X3_TC: 2 = ucn_mlp_x3p.cu (TMEM-resident activations, pipelined; default),
+// 1 = ucn_mlp_x3.cu (round 1: activations in shared memory).  UCN_X3_KERNEL=1 in the environment, or
+// ucn_debug_set_x3_kernel(), selects the older one for A/B timing; both meet the same parity gates.
+static int g_x3_kernel = 0;
+static int x3_kernel() {
+  if (g_x3_kernel == 0) {
+    const char *e = getenv("UCN_X3_KERNEL");
+    g_x3_kernel = (e && e[0] == '1') ? 1 : 2;
+  }
+  return g_x3_kernel;
+}
+extern "C" int ucn_debug_set_x3_kernel(int which) { g_x3_kernel = (which == 1) ? 1 : 2; return UCN_OK; }
+static int mlp_x3_dispatch(const ucn_weights *w, const float *ndc_pts, const float *feat, long long ts, long long ks,
+                           long long rs, const float *angle, int R, int S, float *raw, void *stream) {
+  return x3_kernel() == 1 ? ucn_mlp_forward_x3(w, ndc_pts, feat, ts, ks, rs, angle, R, S, raw, stream)
+                          : ucn_mlp_forward_x3p(w, ndc_pts, feat, ts, ks, rs, angle, R, S, raw, stream);
+}
+
 
 extern "C" int ucn_version(void) { return 100; }
 extern "C" const char *ucn_last_error(void) { return g_err; }
@@ -103,7 +125,7 @@ extern "C" int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const
   if (mode == UCN_MLP_BF16_TC) return ucn_mlp_forward_tc(w, ndc_pts, feat, angle, R, S, raw, stream);
   if (mode == UCN_MLP_BF16X3_TC) {
     const long long F = 24 + 12 * w->V + 1;                       // row-major [N][F] rows (the reference layout)
-    return ucn_mlp_forward_x3(w, ndc_pts, feat, 128 * F, 1, F, angle, R, S, raw, stream);
+    return mlp_x3_dispatch(w, ndc_pts, feat, 128 * F, 1, F, angle, R, S, raw, stream);
   }
   return ucn_set_error(UCN_E_ARG, "ucn_mlp_forward: unknown mode");
 }
@@ -116,7 +138,7 @@ extern "C" int ucn_mlp_forward_tiles(const ucn_weights *w, const float *ndc_pts,
   if (mode != UCN_MLP_BF16X3_TC) return ucn_set_error(UCN_E_UNSUPPORTED, "ucn_mlp_forward_tiles: only UCN_MLP_BF16X3_TC reads tiled rows");
   if (R <= 0) return UCN_OK;
   const long long F = 24 + 12 * w->V + 1;
-  return ucn_mlp_forward_x3(w, ndc_pts, feat_tiles, 128 * F, 128, 1, angle, R, S, raw, stream);
+  return mlp_x3_dispatch(w, ndc_pts, feat_tiles, 128 * F, 128, 1, angle, R, S, raw, stream);
 }
 
 // workspace carve-up for ucn_render_rays (all 256-byte aligned)

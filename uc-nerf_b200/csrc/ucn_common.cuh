@@ -18,6 +18,8 @@
 int ucn_set_error(int code, const char *msg);
 int ucn_cuda_status(cudaError_t e, const char *where);
 void ucn_count_launch(int n = 1);
+void ucn_headw_store(const void *x3_pack, const float *w1024);   // ucn_pack.cu: host copy of K3's head weights per pack
+bool ucn_headw_lookup(const void *x3_pack, float *w1024);
 int ucn_sm_count();            // multiprocessors of the CURRENT device (cached per device)
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: `done` is the caller's static per-device

@@ -4,11 +4,36 @@
 // The reference keeps NCDHW / NCHW maps and samples them with F.grid_sample, i.e. C channel-strided
 // 4-byte loads per texel (utils/utils.py:776-788,859-890).  Channels-last makes a texel one vector load.
 #include <limits.h>
+#include <string.h>
+
+#include <array>
+#include <map>
+#include <mutex>
 
 #include <cuda_bf16.h>
 
 #include "ucn_common.cuh"
 #include "ucn_weights.cuh"
+
+// host copies of the head weights [w_base 128x4 | w_adapt 128x4] per split-bf16 pack (keyed by the pack's device address;
+// refreshed by every ucn_pack_weights into that address)
+namespace {
+std::mutex g_headw_mu;
+std::map<const void *, std::array<float, 1024>> g_headw;
+}  // namespace
+void ucn_headw_store(const void *x3_pack, const float *w1024) {
+  std::lock_guard<std::mutex> lk(g_headw_mu);
+  std::array<float, 1024> a;
+  memcpy(a.data(), w1024, sizeof(float) * 1024);
+  g_headw[x3_pack] = a;
+}
+bool ucn_headw_lookup(const void *x3_pack, float *w1024) {
+  std::lock_guard<std::mutex> lk(g_headw_mu);
+  auto it = g_headw.find(x3_pack);
+  if (it == g_headw.end()) return false;
+  memcpy(w1024, it->second.data(), sizeof(float) * 1024);
+  return true;
+}
 
 namespace {
 
@@ -208,6 +233,12 @@ static int pack_weights_x3(const ucn_state_dict *sd, unsigned char *dst, cudaStr
   ucn_count_launch(2);
   e = cudaGetLastError();
   if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_pack_weights(x3)");
+  // the 4-wide head weights also travel to K3 as a kernel parameter (constant bank): keep a host copy per pack
+  float host[1024];
+  e = cudaMemcpyAsync(host, f32 + X.w_base, sizeof(host), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_pack_weights(x3): head weights");
+  ucn_headw_store(dst, host);
   return UCN_OK;
 }
 
