@@ -188,6 +188,21 @@ int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const float *fea
 /* same network on tile-transposed feature rows (ucn_gather_tiles_from_z); UCN_MLP_BF16X3_TC only */
 int ucn_mlp_forward_tiles(const ucn_weights *w, const float *ndc_pts, const float *feat_tiles, const float *angle,
                           int R, int S, float *raw, int mode, void *stream);
+/* Operand tiles: the interchange format between K2 and the tensor-core MLP (UCN_MLP_BF16X3_TC).  One record of
+ * ucn_operand_tile_bytes(V) bytes per 128-sample tile: [film hi | film lo | img hi | img lo] K-chunks of 128 rows x 8 bf16
+ * (hi = bf16(x), lo = bf16(x - hi); film = mvs feats 24 | (r,g,b,mask) x V | 1 | 0.., img = image feats 8 x V | 1 | 0..,
+ * network/models.py:143-150) followed by the 128 sampled confidences (fp32).  A chunk is already the UMMA K-major
+ * core-matrix layout, so K3 copies it into shared memory / tensor memory verbatim.  V <= 7. */
+size_t ucn_operand_tile_bytes(int V);
+/* K2 writing operand tiles (same gathers as ucn_gather_tiles_from_z; network/renderer.py:177-212) */
+int ucn_gather_operands_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R,
+                               void *operand_tiles, float *ndc_pts, void *stream);
+/* K3 reading operand tiles (network/models.py:138-184): TMEM-resident activations, pipelined rounds */
+int ucn_mlp_forward_operands(const ucn_weights *w, const float *ndc_pts, const void *operand_tiles, const float *angle,
+                             int R, int S, float *raw, int mode, void *stream);
+/* which kernel pair ucn_render_rays uses for UCN_MLP_BF16X3_TC: 2 (default) = operand tiles + ucn_mlp_forward_operands,
+ * 1 = round-1 pair (tile-transposed fp32 rows + ucn_mlp_forward_tiles).  set = 0 queries; returns the current value. */
+int ucn_mlp_x3_variant(int set);
 
 /* ---- K4: alpha compositing -------------------------------------------------------------------
  * replaces raw2alpha / raw2outputs (network/renderer.py:25-36,109-140).  rgb [R][3], depth [R];

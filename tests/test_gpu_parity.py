@@ -524,3 +524,73 @@ def test_row_band_frame_matches_whole_frame():
     fr.set_target(H, W, S, sc.K[0], sc.c2ws[0], sc.w2cs[1], sc.near_fars[0, 0], sc.near_fars[0, 1])
     with pytest.raises(L.UcnError):
         fr.set_row_band(0, 8)
+
+
+@pytest.mark.parametrize("name", ("small_v3", "small_v5", "s126_v3"))
+def test_operand_tiles_match_feature_rows(name):
+    """K2's operand tiles (ucn_gather_operands_from_z: bf16 hi/lo K-chunks the tensor-core MLP copies verbatim) carry
+    exactly the split of the fp32 feature rows K2 writes in its other layouts: hi + lo reproduces every channel to
+    2^-16 relative, hi == bf16(x) bit for bit, ones column and zero padding in place, confidence fp32 verbatim."""
+    import ctypes as C
+    from ucnerf_b200 import lib as L
+    from ucnerf_b200.frame import PackedFrame
+    c = load_case(name)
+    V, S = c["V"], c["S"]
+    fr = PackedFrame.from_scene(c["scene"], S, DEV, dir_switch=c["chunk"])
+    lib = L.load()
+    R = 37                                                            # ragged: the last tile is partial
+    z = T(c["g"]["z"][:R])
+    n = R * S
+    F = fr.F
+    nt = (n + 127) // 128
+    rows = torch.zeros((nt, F, 128), device=DEV)
+    ndc = torch.empty((n, 3), device=DEV)
+    L.check(lib.ucn_gather_tiles_from_z(C.byref(fr.c), L.ptr(z), None, 0, R, L.ptr(rows), L.ptr(ndc), L.stream_ptr()), "tiles")
+    tb = int(lib.ucn_operand_tile_bytes(V))
+    rec = torch.zeros((nt, tb), dtype=torch.uint8, device=DEV)
+    ndc2 = torch.empty((n, 3), device=DEV)
+    L.check(lib.ucn_gather_operands_from_z(C.byref(fr.c), L.ptr(z), None, 0, R, L.ptr(rec), L.ptr(ndc2), L.stream_ptr()), "operands")
+    assert torch.equal(ndc, ndc2)
+    kf, kb = 24 + 4 * V, 8 * V
+    Kf, Kb = (kf + 1 + 15) // 16 * 16, (kb + 1 + 15) // 16 * 16
+    assert tb == (2 * Kf // 8 + 2 * Kb // 8) * 2048 + 512
+    o = 0
+
+    def take(K):
+        nonlocal o
+        t = rec[:, o:o + K // 8 * 2048].contiguous().view(torch.bfloat16).view(nt, K // 8, 128, 8)
+        o += K // 8 * 2048
+        return t.permute(0, 1, 3, 2).reshape(nt, K, 128).float()      # [tile][k][row]
+    fh, fl, ih, il = take(Kf), take(Kf), take(Kb), take(Kb)
+    conf = rec[:, o:].contiguous().view(torch.float32)
+    valid = (torch.arange(nt * 128, device=DEV) < n).view(nt, 1, 128).float()
+    for hi, lo, x, k in ((fh, fl, rows[:, :kf], kf), (ih, il, rows[:, kf:kf + kb], kb)):
+        assert torch.equal(hi[:, :k], x.to(torch.bfloat16).float())   # hi is the bf16 rounding of the fp32 channel
+        assert ((hi + lo)[:, :k] - x).abs().max().item() <= 2.0 ** -16 * max(1.0, x.abs().max().item())
+        assert torch.equal(hi[:, k], valid[:, 0]) and float(lo[:, k].abs().max()) == 0.0          # ones column (bias)
+        assert float(hi[:, k + 1:].abs().max()) == 0.0 and float(lo[:, k + 1:].abs().max()) == 0.0   # K padding
+    assert torch.equal(conf, rows[:, F - 1])
+
+
+def test_round1_x3_kernel_still_meets_the_gate():
+    """ucn_mlp_x3_variant(1): the round-1 kernel pair (tile-transposed fp32 rows) stays selectable and parity-green."""
+    from ucnerf_b200 import lib as L
+    from ucnerf_b200.frame import FrameRenderer, PackedFrame, PackedWeights
+    lib = L.load()
+    assert lib.ucn_mlp_x3_variant(0) in (1, 2)
+    prev = lib.ucn_mlp_x3_variant(0)
+    try:
+        out = {}
+        for variant in (1, 2):
+            assert lib.ucn_mlp_x3_variant(variant) == variant
+            for name in ("s126_v3", "small_v5"):
+                c = load_case(name)
+                fr = PackedFrame.from_scene(c["scene"], c["S"], DEV, dir_switch=c["chunk"])
+                pw = PackedWeights(c["weights"], c["V"], DEV)
+                rgb, _ = FrameRenderer(fr, pw, "bf16").render(t_rand=T(c["t_rand"]))
+                assert np.abs(rgb.cpu().numpy() - c["g"]["rgb"]).max() <= 1e-3, (variant, name)
+                out[(variant, name)] = rgb
+        for name in ("s126_v3", "small_v5"):                          # same arithmetic, different schedule
+            assert (out[(1, name)] - out[(2, name)]).abs().max().item() <= 2e-4
+    finally:
+        lib.ucn_mlp_x3_variant(prev)

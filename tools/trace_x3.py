@@ -16,13 +16,32 @@ ndc = torch.rand((R * S, 3), device="cuda", generator=g)
 NT = (R * S + 127) // 128
 feat = torch.randn((NT, F, 128), device="cuda", generator=g)          # tile-transposed interchange layout
 feat[:, -1, :] = torch.rand((NT, 128), device="cuda", generator=g)
-lib.ucn_mlp_forward_tiles.argtypes = lib.ucn_mlp_forward.argtypes
+if not V1:
+    # operand tiles of the same rows (ucn_gather.cu): [film hi | film lo | img hi | img lo] chunks of [128][8] bf16 + confidence
+    kf, kb = 24 + 4 * V, 8 * V
+    Kf, Kb = (kf + 1 + 15) // 16 * 16, (kb + 1 + 15) // 16 * 16
+    def chunks(x, K):                                                 # x [NT, k, 128] fp32 -> hi, lo [NT, K/8, 128, 8] bf16
+        pad = torch.zeros((NT, K, 128), device="cuda")
+        pad[:, :x.shape[1]] = x
+        pad[:, x.shape[1]] = 1.0
+        hi = pad.to(torch.bfloat16)
+        lo = (pad - hi.float()).to(torch.bfloat16)
+        f = lambda t: t.view(NT, K // 8, 8, 128).permute(0, 1, 3, 2).contiguous()
+        return f(hi), f(lo)
+    fh, fl = chunks(feat[:, :kf], Kf)
+    ih, il = chunks(feat[:, kf:kf + kb], Kb)
+    rec = torch.cat([t.view(torch.uint8).reshape(NT, -1) for t in (fh, fl, ih, il)] +
+                    [feat[:, -1, :].contiguous().view(torch.uint8).reshape(NT, -1)], dim=1).contiguous()
+    assert rec.shape[1] == lib.ucn_operand_tile_bytes(V)
 ang = torch.randn((R, 3), device="cuda", generator=g)
 raw = torch.empty((R * S, 4), device="cuda")
 CAP = 2048
 buf = torch.zeros(7 * CAP * 2, dtype=torch.int64, device="cuda")
 def run():
-    L.check(lib.ucn_mlp_forward_tiles(C.byref(pw.c), L.ptr(ndc), L.ptr(feat), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
+    if V1:
+        L.check(lib.ucn_mlp_forward_tiles(C.byref(pw.c), L.ptr(ndc), L.ptr(feat), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
+    else:
+        L.check(lib.ucn_mlp_forward_operands(C.byref(pw.c), L.ptr(ndc), L.ptr(rec), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
 flags = int(os.environ.get("X3_DBG", "0"))
 L.check((lib.ucn_debug_set_flags if V1 else lib.ucn_debug_set_flags_p)(flags), "flags")
 run(); torch.cuda.synchronize()

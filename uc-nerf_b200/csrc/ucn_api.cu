@@ -40,12 +40,12 @@ int ucn_mlp_forward_tc(const ucn_weights *w, const float *ndc_pts, const float *
 int ucn_mlp_forward_x3(const ucn_weights *w, const float *ndc_pts, const float *feat, long long f_tile_stride,
                        long long f_k_stride, long long f_row_stride, const float *angle, int R, int S, float *raw,
                        void *stream);
-int ucn_mlp_forward_x3p(const ucn_weights *w, const float *ndc_pts, const float *feat, long long f_tile_stride,
-                       long long f_k_stride, long long f_row_stride, const float *angle, int R, int S, float *raw,
-                       void *stream);
-// Which split-bf16 kernel serves UCN_MLP_BF16X3_TC: 2 = ucn_mlp_x3p.cu (TMEM-resident activations, pipelined; default),
-// 1 = ucn_mlp_x3.cu (round 1: activations in shared memory).  UCN_X3_KERNEL=1 in the environment, or
-// ucn_debug_set_x3_kernel(), selects the older one for A/B timing; both meet the same parity gates.
+int ucn_mlp_forward_x3p(const ucn_weights *w, const float *ndc_pts, const void *operand_tiles, const float *angle, int R,
+                        int S, float *raw, void *stream);
+// Which split-bf16 kernel the fused frame path (ucn_render_rays) uses for UCN_MLP_BF16X3_TC:
+//   2 = ucn_mlp_x3p.cu (default): TMEM-resident activations, pipelined; reads K2's operand tiles (ucn_gather_operands_from_z)
+//   1 = ucn_mlp_x3.cu (round 1): activations in shared memory; reads tile-transposed or row-major fp32 feature rows
+// UCN_X3_KERNEL=1 in the environment or ucn_mlp_x3_variant(1) selects the older pair for A/B timing; both meet the gates.
 static int g_x3_kernel = 0;
 static int x3_kernel() {
   if (g_x3_kernel == 0) {
@@ -54,13 +54,10 @@ static int x3_kernel() {
   }
   return g_x3_kernel;
 }
-extern "C" int ucn_debug_set_x3_kernel(int which) { g_x3_kernel = (which == 1) ? 1 : 2; return UCN_OK; }
-static int mlp_x3_dispatch(const ucn_weights *w, const float *ndc_pts, const float *feat, long long ts, long long ks,
-                           long long rs, const float *angle, int R, int S, float *raw, void *stream) {
-  return x3_kernel() == 1 ? ucn_mlp_forward_x3(w, ndc_pts, feat, ts, ks, rs, angle, R, S, raw, stream)
-                          : ucn_mlp_forward_x3p(w, ndc_pts, feat, ts, ks, rs, angle, R, S, raw, stream);
+extern "C" int ucn_mlp_x3_variant(int set) {
+  if (set == 1 || set == 2) g_x3_kernel = set;
+  return x3_kernel();
 }
-
 
 extern "C" int ucn_version(void) { return 100; }
 extern "C" const char *ucn_last_error(void) { return g_err; }
@@ -125,7 +122,7 @@ extern "C" int ucn_mlp_forward(const ucn_weights *w, const float *ndc_pts, const
   if (mode == UCN_MLP_BF16_TC) return ucn_mlp_forward_tc(w, ndc_pts, feat, angle, R, S, raw, stream);
   if (mode == UCN_MLP_BF16X3_TC) {
     const long long F = 24 + 12 * w->V + 1;                       // row-major [N][F] rows (the reference layout)
-    return mlp_x3_dispatch(w, ndc_pts, feat, 128 * F, 1, F, angle, R, S, raw, stream);
+    return ucn_mlp_forward_x3(w, ndc_pts, feat, 128 * F, 1, F, angle, R, S, raw, stream);
   }
   return ucn_set_error(UCN_E_ARG, "ucn_mlp_forward: unknown mode");
 }
@@ -138,7 +135,17 @@ extern "C" int ucn_mlp_forward_tiles(const ucn_weights *w, const float *ndc_pts,
   if (mode != UCN_MLP_BF16X3_TC) return ucn_set_error(UCN_E_UNSUPPORTED, "ucn_mlp_forward_tiles: only UCN_MLP_BF16X3_TC reads tiled rows");
   if (R <= 0) return UCN_OK;
   const long long F = 24 + 12 * w->V + 1;
-  return mlp_x3_dispatch(w, ndc_pts, feat_tiles, 128 * F, 128, 1, angle, R, S, raw, stream);
+  return ucn_mlp_forward_x3(w, ndc_pts, feat_tiles, 128 * F, 128, 1, angle, R, S, raw, stream);
+}
+
+extern "C" int ucn_mlp_forward_operands(const ucn_weights *w, const float *ndc_pts, const void *operand_tiles,
+                                        const float *angle, int R, int S, float *raw, int mode, void *stream) {
+  UCN_CHECK_ARG(w && ndc_pts && operand_tiles && angle && raw, "ucn_mlp_forward_operands: null argument");
+  UCN_CHECK_ARG(w->V >= 1 && w->V <= 7, "ucn_mlp_forward_operands: 1 <= V <= 7");
+  UCN_CHECK_ARG(S > 0, "ucn_mlp_forward_operands: S <= 0");
+  if (mode != UCN_MLP_BF16X3_TC) return ucn_set_error(UCN_E_UNSUPPORTED, "ucn_mlp_forward_operands: only UCN_MLP_BF16X3_TC reads operand tiles");
+  if (R <= 0) return UCN_OK;
+  return ucn_mlp_forward_x3p(w, ndc_pts, operand_tiles, angle, R, S, raw, stream);
 }
 
 // workspace carve-up for ucn_render_rays (all 256-byte aligned)
@@ -150,7 +157,8 @@ struct Workspace {
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 255) & ~size_t(255); return r; };
     z = take(N * 4); rays_d = take((size_t)R * 12); angle = take((size_t)R * 12);
-    ndc = take(N * 12); feat = take(((N + 127) / 128) * 128 * F * 4); raw = take(N * 16);   // feat: whole tiles
+    const size_t tiles = (N + 127) / 128, rows_b = 128 * F * 4, oper_b = ucn_operand_tile_bytes(f->V);
+    ndc = take(N * 12); feat = take(tiles * (rows_b > oper_b ? rows_b : oper_b)); raw = take(N * 16);   // whole tiles, either layout
     total = o;
   }
 };
@@ -177,7 +185,10 @@ extern "C" int ucn_render_rays(const ucn_frame *f, const ucn_weights *w, int ray
   int rc;
   if ((rc = ucn_raygen_sample(f, nullptr, ray0, R, t_vals, t_rand, seed, z, rays_d, nullptr, nullptr, stream))) return rc;
   if ((rc = ucn_dir_feature(f, rays_d, R, ray0, angle, stream))) return rc;
-  if (mode == UCN_MLP_BF16X3_TC) {          // tensor-core path: tile-transposed interchange rows
+  if (mode == UCN_MLP_BF16X3_TC && x3_kernel() == 2 && f->V <= 7) {   // tensor-core path: K2 writes the MLP's operand tiles
+    if ((rc = ucn_gather_operands_from_z(f, z, nullptr, ray0, R, feat, ndc, stream))) return rc;
+    if ((rc = ucn_mlp_forward_operands(w, ndc, feat, angle, R, f->S, raw, mode, stream))) return rc;
+  } else if (mode == UCN_MLP_BF16X3_TC) {   // round-1 kernel: tile-transposed fp32 interchange rows
     if ((rc = ucn_gather_tiles_from_z(f, z, nullptr, ray0, R, feat, ndc, stream))) return rc;
     if ((rc = ucn_mlp_forward_tiles(w, ndc, feat, angle, R, f->S, raw, mode, stream))) return rc;
   } else {

@@ -42,8 +42,8 @@ __device__ __forceinline__ void fma8(Acc8 &a, const float *__restrict__ texel, f
 // Branch-free: where the reference skips an out-of-range corner (ATen within_bounds test), the corner index is clamped
 // instead and its weight is exactly 0 there (the coordinate was clipped to size-1, so w1 = x - floor(x) = 0): the
 // fma adds +0.  32-bit texel indices (launcher checks every map has < 2^28 texels).
-__device__ __forceinline__ void tri8(const float *__restrict__ vol, int D, int h, int w, float cx, float cy, float cz,
-                                     float *__restrict__ out, int os, int32_t *__restrict__ idx) {
+__device__ __forceinline__ Acc8 tri8(const float *__restrict__ vol, int D, int h, int w, float cx, float cy, float cz,
+                                     int32_t *__restrict__ idx) {
   const ucn::Lerp1 ax = ucn::axis(ucn::to_grid(cx), w, false);
   const ucn::Lerp1 ay = ucn::axis(ucn::to_grid(cy), h, false);
   const ucn::Lerp1 az = ucn::axis(ucn::to_grid(cz), D, false);
@@ -59,12 +59,40 @@ __device__ __forceinline__ void tri8(const float *__restrict__ vol, int D, int h
     const uint32_t t = col00 + ((dy ? y1 : 0u) + (dx ? x1 : 0u)) * Du + (dz ? z1 : 0u);
     fma8(a, vol + (size_t)t * 8, wgt);
   }
-#pragma unroll
-  for (int c = 0; c < 8; ++c) out[c * os] = a.v[c];
+  return a;
 }
 
-template <bool FROM_Z, bool TILED>
-__global__ void __launch_bounds__(kThreads, TILED ? 8 : 7)
+// ---- operand tiles (OUT = 2): what the tensor-core MLP's shared-memory / TMEM operands are made of -----------------
+// One 128-sample tile = one record of ucn_operand_tile_bytes(V) bytes:
+//   film hi | film lo   Kfilm/8 chunks each: [mvs feats 24 | (r,g,b,mask) x V | 1 | 0...]   (models.py:143-150)
+//   img  hi | img  lo   Kfb/8 chunks each:   [img feats 8 x V | 1 | 0...]                  (models.py:147)
+//   confidence          128 fp32                                                            (models.py:149)
+// a chunk = 8 consecutive K values of the 128 rows as bf16, [row][8] (2 KB) -- the UMMA no-swizzle K-major core-matrix
+// layout, so K3 copies chunks verbatim (cp.async / 128-bit loads); hi = bf16(x), lo = bf16(x - hi), the split K3's
+// round-1 kernel did itself.  The "1" is the ones column that folds the layer's bias into the MMA.
+struct OperGeom { int kf8, kb8; };
+__device__ __forceinline__ OperGeom oper_geom(int V) {
+  return {((24 + 4 * V + 1 + 15) & ~15) / 8, ((8 * V + 1 + 15) & ~15) / 8};
+}
+__device__ __forceinline__ uint32_t bf2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ void emit_chunk(unsigned char *__restrict__ hi_base, unsigned char *__restrict__ lo_base, int chunk,
+                                           const float *v) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    h[i] = bf2(v[2 * i], v[2 * i + 1]);
+    l[i] = bf2(v[2 * i] - __uint_as_float(h[i] << 16), v[2 * i + 1] - __uint_as_float(h[i] & 0xFFFF0000u));
+  }
+  *reinterpret_cast<uint4 *>(hi_base + (size_t)chunk * 2048) = make_uint4(h[0], h[1], h[2], h[3]);
+  *reinterpret_cast<uint4 *>(lo_base + (size_t)chunk * 2048) = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+template <bool FROM_Z, int OUT>        // OUT: 0 row-major [N][F], 1 tile-transposed [tile][F][128], 2 operand tiles
+__global__ void __launch_bounds__(kThreads, OUT ? 8 : 7)
 gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts_or_z,
               const float *__restrict__ ndc1, const float *__restrict__ ndc2, const float *__restrict__ ndc3,
               const float *__restrict__ pix_yx, int ray0, int R, int64_t n_samples, int parts,
@@ -76,8 +104,15 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
   // [F][128] tile of this block in global memory
   // (TILED is a template parameter so that the 61 channel stores compile to STG / STS instead of generic ST, and the
   //  tiled instance, which needs no shared memory, is held to 64 registers: 8 blocks per SM instead of 7)
+  constexpr bool TILED = OUT == 1, OPER = OUT == 2;
   constexpr int os = TILED ? kThreads : 1;
   float *row = TILED ? feat + (int64_t)blockIdx.x * F * kThreads + threadIdx.x : rows + (size_t)threadIdx.x * ld;
+  const OperGeom og = oper_geom(V);
+  unsigned char *rec = reinterpret_cast<unsigned char *>(feat) + (size_t)blockIdx.x * ((2 * og.kf8 + 2 * og.kb8) * 2048 + 512) +
+                       threadIdx.x * 16;                       // this row's 16 bytes of chunk 0 of the tile's record
+  unsigned char *film_hi = rec, *film_lo = rec + og.kf8 * 2048, *img_hi = rec + 2 * og.kf8 * 2048,
+                *img_lo = img_hi + og.kb8 * 2048;
+  float cbuf[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};          // OPER: (r,g,b,mask) of two views = one film chunk
   if (q < n_samples) {
     const float iw = (float)(f.W - 1), ih = (float)(f.H - 1);
     float p[3], c1[3], c2[3], c3[3];
@@ -109,14 +144,21 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
       }
     }
     int32_t *ir = idx_out ? idx_out + q * (11 + 3 * V) : nullptr;
-    if (parts != UCN_PART_ALL) {
+    if (!OPER && parts != UCN_PART_ALL) {
       for (int c = 0; c < F; ++c) row[c * os] = 0.0f;
       if (ir) for (int c = 0; c < 11 + 3 * V; ++c) ir[c] = 0;
     }
     if (parts & UCN_PART_VOLUMES) {
-    tri8(f.vol[0], f.D[0], f.h[0], f.w[0], c1[0], c1[1], c1[2], row, os, ir);
-    tri8(f.vol[1], f.D[1], f.h[1], f.w[1], c2[0], c2[1], c2[2], row + 8 * os, os, ir ? ir + 3 : nullptr);
-    tri8(f.vol[2], f.D[2], f.h[2], f.w[2], c3[0], c3[1], c3[2], row + 16 * os, os, ir ? ir + 6 : nullptr);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float *cc = k == 0 ? c1 : (k == 1 ? c2 : c3);
+      const Acc8 a = tri8(f.vol[k], f.D[k], f.h[k], f.w[k], cc[0], cc[1], cc[2], ir ? ir + 3 * k : nullptr);
+      if (OPER) emit_chunk(film_hi, film_lo, k, a.v);
+      else {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) row[(8 * k + c) * os] = a.v[c];
+      }
+    }
     {   // confidence: depth-1 "volume" => bilinear, align_corners=False (renderer.py:195, utils.py:859-865)
       const ucn::Lerp1 ax = ucn::axis(ucn::to_grid(c3[0]), f.W, false), ay = ucn::axis(ucn::to_grid(c3[1]), f.H, false);
       float acc = 0.0f;
@@ -127,7 +169,8 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
         const uint32_t t = t00 + ((dy && ay.has1) ? (uint32_t)f.W : 0u) + ((dx && ax.has1) ? 1u : 0u);
         acc = fmaf(__ldg(f.conf + t), __fmul_rn(dx ? ax.w1 : ax.w0, dy ? ay.w1 : ay.w0), acc);
       }
-      row[(F - 1) * os] = acc;
+      if (OPER) reinterpret_cast<float *>(rec - threadIdx.x * 16 + (2 * og.kf8 + 2 * og.kb8) * 2048)[threadIdx.x] = acc;
+      else row[(F - 1) * os] = acc;
       if (ir) { ir[9] = ax.i0; ir[10] = ay.i0; }
     }
     }
@@ -151,13 +194,41 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
         c.x = fmaf(px.x, wgt, c.x); c.y = fmaf(px.y, wgt, c.y); c.z = fmaf(px.z, wgt, c.z);
         fma8(a, ft + t * 8, wgt);
       }
-      float *o = row + (24 + 4 * v) * os;
-      o[0] = c.x; o[os] = c.y; o[2 * os] = c.z; o[3 * os] = m;
-      float *of = row + (24 + 4 * V + 8 * v) * os;
+      if (OPER) {
+        const int h4 = (v & 1) * 4;
+        cbuf[h4] = c.x; cbuf[h4 + 1] = c.y; cbuf[h4 + 2] = c.z; cbuf[h4 + 3] = m;
+        if (v & 1) emit_chunk(film_hi, film_lo, 3 + (v >> 1), cbuf);
+        emit_chunk(img_hi, img_lo, v, a.v);
+      } else {
+        float *o = row + (24 + 4 * v) * os;
+        o[0] = c.x; o[os] = c.y; o[2 * os] = c.z; o[3 * os] = m;
+        float *of = row + (24 + 4 * V + 8 * v) * os;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) of[k * os] = a.v[k];
+        for (int k = 0; k < 8; ++k) of[k * os] = a.v[k];
+      }
       if (ir) { ir[11 + 3 * v] = ax.i0; ir[12 + 3 * v] = ay.i0; ir[13 + 3 * v] = (int32_t)m; }
     }
+  }
+  if (OPER) {
+    // the ones column (bias) closes the film / img operands; K padding and the rows past the last sample are zeros
+    const float zero8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (q < n_samples) {
+      float tail[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      int kc = 3 + (V >> 1);
+      if (V & 1) {                                           // last view sits in the low half of its chunk; the 1 follows it
+        tail[0] = cbuf[0]; tail[1] = cbuf[1]; tail[2] = cbuf[2]; tail[3] = cbuf[3]; tail[4] = 1.0f;
+      } else tail[0] = 1.0f;
+      emit_chunk(film_hi, film_lo, kc, tail);
+      for (++kc; kc < og.kf8; ++kc) emit_chunk(film_hi, film_lo, kc, zero8);
+      const float one8[8] = {1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      emit_chunk(img_hi, img_lo, V, one8);
+      for (kc = V + 1; kc < og.kb8; ++kc) emit_chunk(img_hi, img_lo, kc, zero8);
+    } else {
+      for (int kc = 0; kc < og.kf8; ++kc) emit_chunk(film_hi, film_lo, kc, zero8);
+      for (int kc = 0; kc < og.kb8; ++kc) emit_chunk(img_hi, img_lo, kc, zero8);
+      reinterpret_cast<float *>(rec - threadIdx.x * 16 + (2 * og.kf8 + 2 * og.kb8) * 2048)[threadIdx.x] = 0.0f;
+    }
+    return;
   }
   if (TILED) {
     // tile-transposed rows for the tensor-core MLP: block == one 128-sample tile, laid out [F][128] so that both
@@ -192,18 +263,20 @@ static int launch_gather(bool from_z, const ucn_frame *f, const float *a, const 
   const cudaStream_t st = (cudaStream_t)stream;
   static int attr_a[kUcnMaxDevices], attr_b[kUcnMaxDevices];
   if (!tiled) {
-    cudaError_t e = ucn_ensure_dyn_smem(gather_kernel<true, false>, 100 * 1024, attr_a);
-    if (e == cudaSuccess) e = ucn_ensure_dyn_smem(gather_kernel<false, false>, 100 * 1024, attr_b);
+    cudaError_t e = ucn_ensure_dyn_smem(gather_kernel<true, 0>, 100 * 1024, attr_a);
+    if (e == cudaSuccess) e = ucn_ensure_dyn_smem(gather_kernel<false, 0>, 100 * 1024, attr_b);
     if (e != cudaSuccess) return ucn_cuda_status(e, "gather smem attribute");
   }
-  if (from_z && tiled)
-    gather_kernel<true, true><<<blocks, kThreads, 0, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
+  if (from_z && tiled == 2)
+    gather_kernel<true, 2><<<blocks, kThreads, 0, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
+  else if (from_z && tiled)
+    gather_kernel<true, 1><<<blocks, kThreads, 0, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
   else if (from_z)
-    gather_kernel<true, false><<<blocks, kThreads, smem, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
+    gather_kernel<true, 0><<<blocks, kThreads, smem, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
   else if (tiled)
-    gather_kernel<false, true><<<blocks, kThreads, 0, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
+    gather_kernel<false, 1><<<blocks, kThreads, 0, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
   else
-    gather_kernel<false, false><<<blocks, kThreads, smem, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
+    gather_kernel<false, 0><<<blocks, kThreads, smem, st>>>(*f, a, n1, n2, n3, pix_yx, ray0, R, n, parts, feat, ndc_out, idx);
   UCN_LAUNCH_CHECK("gather_kernel");
   return UCN_OK;
 }
@@ -229,6 +302,19 @@ extern "C" int ucn_gather_tiles_from_z(const ucn_frame *f, const float *z, const
   UCN_CHECK_ARG(f && f->S > 0, "ucn_gather_tiles_from_z: bad frame");
   return launch_gather(true, f, z, nullptr, nullptr, nullptr, pix_yx, ray0, R, (int64_t)R * f->S, UCN_PART_ALL, 1,
                        feat_tiles, ndc_pts, nullptr, stream);
+}
+
+extern "C" size_t ucn_operand_tile_bytes(int V) {
+  const int kf8 = ((24 + 4 * V + 1 + 15) & ~15) / 8, kb8 = ((8 * V + 1 + 15) & ~15) / 8;
+  return (size_t)(2 * kf8 + 2 * kb8) * 2048 + 512;
+}
+
+extern "C" int ucn_gather_operands_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R,
+                                          void *operand_tiles, float *ndc_pts, void *stream) {
+  UCN_CHECK_ARG(f && f->S > 0, "ucn_gather_operands_from_z: bad frame");
+  UCN_CHECK_ARG(f->V <= 7, "ucn_gather_operands_from_z: the tensor-core MLP takes at most 7 source views");
+  return launch_gather(true, f, z, nullptr, nullptr, nullptr, pix_yx, ray0, R, (int64_t)R * f->S, UCN_PART_ALL, 2,
+                       static_cast<float *>(operand_tiles), ndc_pts, nullptr, stream);
 }
 
 namespace {

@@ -55,7 +55,7 @@ constexpr int NROUND = 10;
 constexpr int MAXBLK = 48;
 
 __device__ long long *g_trace_p = nullptr;   // CTA-0 timeline (tools/trace_x3.py), off unless a buffer is set
-__device__ int g_dbg_p = 0;                  // reserved for timing experiments (tools/trace_x3.py X3_DBG); unused by the shipped code
+__device__ int g_dbg_p = 0;                  // timing experiments (tools/trace_x3.py X3_DBG); 0 in production
 constexpr int kTraceCap = 2048;
 struct Tracer {
   long long *base; int n;
@@ -81,7 +81,7 @@ struct Plan {
   uint8_t round_begin[NROUND + 1];
   uint8_t a_reg[NROUND];                     // TS rounds: A region (0 = P, 1 = Q)
   uint8_t nblk, nst, rpt, pad;
-  uint32_t off_f32, off_exch, off_rayb, off_bars, smem_total;
+  uint32_t off_f32, off_exch, off_rayb, off_ubuf, off_bars, smem_total;
 };
 
 // (v0..v15) -> one K16 unit of the TMEM A operand: 8 words of bf16 hi pairs, then 8 words of lo pairs
@@ -193,12 +193,12 @@ __device__ __forceinline__ void epi32(uint32_t t_d, uint32_t t_other, const floa
         }
       }
     }
-    if (MODE != 2) {
-      uint32_t w[16];
-      split16(v, w);
-      tmem_st16(t_d + c0 + 16 * u, w);
+    if (MODE != 2) {                                       // the unit's accumulator words are dead: reuse them for the operand
+#pragma unroll
+      for (int i = 0; i < 8; ++i) split2(v[2 * i], v[2 * i + 1], a[16 * u + i], a[16 * u + 8 + i]);
     }
   }
+  if (MODE != 2) tmem_st32(t_d + c0, a);                   // one 4 KB store per warp and chunk
 }
 
 // both 32-column chunks of a warpgroup (hf 0: columns 0..31 and 64..95, hf 1: 32..63 and 96..127), optionally handing each
@@ -206,7 +206,7 @@ __device__ __forceinline__ void epi32(uint32_t t_d, uint32_t t_other, const floa
 #define EPI_LOOP(MODE, TD, TO, BIAS, HANDOFF)                                                       \
   do {                                                                                              \
     _Pragma("unroll 1") for (int h2 = 0; h2 < 2; ++h2) {                                            \
-      epi32<MODE, false, -1>(TD, TO, BIAS, nullptr, mod_row, hw.base, head, h2 ? cB : cA);          \
+      if (!(dbg & 1)) epi32<MODE, false, -1>(TD, TO, BIAS, nullptr, mod_row, hw.base, head, h2 ? cB : cA); \
       if (HANDOFF) arrive(h2 ? goB : goA);                                                          \
     }                                                                                               \
   } while (0)
@@ -225,23 +225,27 @@ struct HeadW { float base[512], adapt[512]; };   // [column][4]: confi_rgb|alpha
 
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW hw, const unsigned char *__restrict__ wpack, int V,
-               const float *__restrict__ ndc_pts, const float *__restrict__ feat, long long f_tile_stride,
-               long long f_k_stride, long long f_row_stride, const float *__restrict__ rayterm, long long N, int S,
-               float *__restrict__ raw, uint4 *__restrict__ pe_stash) {
+               const float *__restrict__ ndc_pts, const unsigned char *__restrict__ oper, long long rec_bytes,
+               const float *__restrict__ rayterm, long long N, int S, float *__restrict__ raw,
+               uint4 *__restrict__ pe_stash) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const ucn::X3Layout L(V);
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int nst = plan.nst, rpt = plan.rpt, nblk = plan.nblk;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t ring = sbase + 2 * MODB;
-  // barriers: go[2][4] (count 4: the warps of the warpgroup that owns the chunk), acc[2] (count 1), wfull/wempty[nst]
+  // barriers: go[2][4] (count 4: the warps of the warpgroup that owns the chunk), acc[2] (count 1), wfull/wempty[nst];
+  // stager hand-shake per slot: modfree (count 8: every epilogue warp after its last FiLM read of the tile), r7 (count 1:
+  // fb's MMAs done, tcgen05.commit), staged (count 2: both stager warps)
   const uint32_t bar_go = pin(sbase + plan.off_bars), bar_acc = pin(bar_go + 64), bar_wfull = pin(bar_acc + 16),
-                 bar_wempty = pin(bar_wfull + 8 * nst), tmem_ptr_addr = bar_wempty + 8 * nst;
+                 bar_wempty = pin(bar_wfull + 8 * nst), bar_modfree = pin(bar_wempty + 8 * nst), bar_r7 = pin(bar_modfree + 16),
+                 bar_staged = pin(bar_r7 + 16), tmem_ptr_addr = bar_staged + 16;
+  float *ubuf_s = reinterpret_cast<float *>(smem + plan.off_ubuf);      // [slot][tile parity][row]: 1 - confidence
   float *f32s = reinterpret_cast<float *>(smem + plan.off_f32);
   float4 *exch_s = reinterpret_cast<float4 *>(smem + plan.off_exch);
   float *rayb_s = reinterpret_cast<float *>(smem + plan.off_rayb);
   __shared__ uint32_t blk_s[MAXBLK], goff_s[MAXBLK];
-  const int F = 24 + 12 * V + 1, Kfilm_real = 24 + 4 * V, Kfb_real = 8 * V;
+  const int Kf8 = L.Kfilm / 8, Kb8 = L.Kfb / 8;               // K-chunks of the film / img operands (ucn_gather.cu: operand tiles)
   const float *f32g = reinterpret_cast<const float *>(wpack + L.f32);
 
   // ---- one-time setup ---------------------------------------------------------------------------
@@ -255,6 +259,7 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
     for (int i = 0; i < 8; ++i) mbar_init(bar_go + 8 * i, 4);
     mbar_init(bar_acc, 1); mbar_init(bar_acc + 8, 1);
     for (int i = 0; i < nst; ++i) { mbar_init(bar_wfull + 8 * i, 1); mbar_init(bar_wempty + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_modfree + 8 * i, 8); mbar_init(bar_r7 + 8 * i, 1); mbar_init(bar_staged + 8 * i, 2); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) tmem_alloc512(tmem_ptr_addr);
@@ -290,7 +295,7 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
     const uint64_t dt = umma_desc(0, CHUNK, 128);                 // LBO = 2048 (K-chunks of A, tiles of B), SBO = 128
     const uint32_t dhi = (uint32_t)(dt >> 32), dlo = (uint32_t)dt;
     auto mk = [&](uint32_t lo) { return ((uint64_t)dhi << 32) | lo; };
-    uint32_t st0 = 0, wph0 = 0, ph_go0 = 0, ph_go1 = 0;
+    uint32_t st0 = 0, wph0 = 0, ph_go0 = 0, ph_go1 = 0, ph_staged = 0;
     Tracer tr(0);
     if (lane != 0) tr.base = nullptr;
     const uint32_t ring_lo = dlo + (ring >> 4);
@@ -303,6 +308,7 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
 #pragma unroll 1
         for (int s = 0; s < nslots; ++s) {
           const uint32_t go = bar_go + 32 * s, ph = s ? ph_go1 : ph_go0;
+          if (r == 0) mbar_wait(bar_staged + 8 * s, ph_staged);   // the stager warps have placed this tile's operands
           tr.ev(1, r, s);
           const uint32_t a_ss = dlo + ((sbase + s * MODB) >> 4);
           const uint32_t t_slot = tmem_base + s * 256;
@@ -352,13 +358,91 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
             if (++st == (uint32_t)nst) { st = 0; wph ^= 1; }
           }
           umma_commit_w(bar_acc + 8 * s);
+          if (r == 7) umma_commit_w(bar_r7 + 8 * s);              // fb has read the image features: chunks 0..15 are free
           if (s) ph_go1 ^= 1; else ph_go0 ^= 1;
           if (s == nslots - 1) { st0 = st; wph0 = wph; }
           tr.ev(2, r, s, (w_go << 20) | (w_full & 0xFFFFF));
         }
+        if (r == 0) ph_staged ^= 1;
       }
     }
     __syncwarp();
+  } else if (warp == 2 || warp == 3) {
+    // ================= stager warps =================================================================
+    // Everything a tile reads from global memory except the image features is brought in HERE, off the epilogue warps'
+    // serial chain (a global load issued under this kernel's shared-memory / TMEM traffic takes 2-3 K cycles, a PE
+    // rebuild ~4 K): per tile k of slot s and row,
+    //   (a) any time:                  x -> PE(x) as bf16 hi/lo words -> global stash[parity] (L2); 1 - confidence -> ubuf
+    //   (b) after tile k-1's last FiLM epilogue (modfree):  [film inputs | 1] chunks (K2's operand tile) -> chunks 16.. /
+    //       24.. of the slot's 64 KB by cp.async: no registers, all copies of a slot in flight at once
+    //   (c) after tile k-1's fb MMAs (r7):                  stash -> chunks 0..7 / 8..15 (the shared-memory operand of L0)
+    // then `staged`.  Each lane serves two rows of each slot (warp 2: rows 0..63, warp 3: 64..127).
+    const uint32_t Nu = (uint32_t)N;
+    uint32_t ph_mod = 0, ph_r7w = 0;                             // both slots advance in lock step
+    for (long long k = 0;; ++k) {
+      const long long t0 = 2ll * (blockIdx.x + k * gridDim.x);
+      if (t0 >= ntiles) break;
+      const int nsl = (t0 + 1 < ntiles) ? 2 : 1;
+      const int par = (int)(k & 1);
+#pragma unroll 1
+      for (int sl = 0; sl < nsl; ++sl) {                          // (a)
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+          const int row = (warp - 2) * 64 + 32 * h + lane;
+          const uint32_t q = (uint32_t)(t0 + sl) * 128u + row;
+          const bool valid = q < Nu;
+          float x[3] = {0.f, 0.f, 0.f};
+          if (valid) { x[0] = __ldg(ndc_pts + 3 * q); x[1] = __ldg(ndc_pts + 3 * q + 1); x[2] = __ldg(ndc_pts + 3 * q + 2); }
+          const float *conf = reinterpret_cast<const float *>(oper + (t0 + sl) * rec_bytes + (size_t)(2 * Kf8 + 2 * Kb8) * 2048);
+          ubuf_s[(sl * 2 + par) * 128 + row] = 1.0f - __ldg(conf + row);                                     // models.py:149
+          float pe[64];
+          pos_enc<10>(x, pe);
+          pe[63] = 0.0f;
+          uint4 *st4 = pe_stash + (((size_t)blockIdx.x * 2 + sl) * 2 + par) * 16 * 128 + row;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) split2(pe[8 * c + 2 * i], pe[8 * c + 2 * i + 1], hi[i], lo[i]);
+            st4[c * 128] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            st4[(8 + c) * 128] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          }
+        }
+      }
+#pragma unroll 1
+      for (int sl = 0; sl < nsl; ++sl) {
+        const uint32_t mod_s = sbase + sl * MODB;
+        if (k > 0) mbar_wait_backoff(bar_modfree + 8 * sl, ph_mod);          // (b)
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {                              // K2 wrote the operand chunks: copy them verbatim
+          const int row = (warp - 2) * 64 + 32 * h + lane;
+          const unsigned char *rec = oper + (t0 + sl) * rec_bytes + row * 16;
+#pragma unroll 1
+          for (int c = 0; c < Kf8; ++c) {
+            cp_async16(mod_s + (16 + c) * CHUNK + row * 16, rec + (size_t)c * 2048);
+            cp_async16(mod_s + (24 + c) * CHUNK + row * 16, rec + (size_t)(Kf8 + c) * 2048);
+          }
+        }
+        cp_async_commit();
+        if (k > 0) mbar_wait_backoff(bar_r7 + 8 * sl, ph_r7w);               // (c)
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+          const int row = (warp - 2) * 64 + 32 * h + lane;
+          const uint4 *st4 = pe_stash + (((size_t)blockIdx.x * 2 + sl) * 2 + par) * 16 * 128 + row;
+          uint4 w[16];
+#pragma unroll
+          for (int c = 0; c < 16; ++c) w[c] = st4[c * 128];                  // this thread's own stores (a)
+#pragma unroll
+          for (int c = 0; c < 16; ++c) sts128(mod_s + row * 16 + c * CHUNK, w[c].x, w[c].y, w[c].z, w[c].w);
+        }
+        cp_async_wait_all();
+        __threadfence();                                           // stash and ubuf are read by the epilogue warps
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_staged + 8 * sl);
+      }
+      if (k > 0) { ph_mod ^= 1; ph_r7w ^= 1; }
+    }
   } else if (warp >= 4) {
     // ================= epilogue warpgroups =========================================================
     const int g = (warp - 4) >> 2, s = g >> 1, hf = g & 1;
@@ -373,7 +457,8 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
     uint32_t ph_acc = 0;
     Tracer tr(((warp & 3) == 0 && lane == 0) ? 1 + g : 6);
     if (!((warp & 3) == 0 && lane == 0)) tr.base = nullptr;
-    float head[4], base4[4] = {0.f, 0.f, 0.f, 0.f};
+    float head[4], base4[4] = {0.f, 0.f, 0.f, 0.f}, u_cur = 0.f;
+    const int dbg = g_dbg_p;             // timing experiment (results wrong): 1 = skip the 128-wide epilogues of rounds 0-4, 7, 8
 
     // hand a chunk (TMEM operand) / everything (shared-memory operands) to the MMA issuer
     auto arrive = [&](uint32_t bar) {
@@ -390,7 +475,7 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
       if (lane == 0) { mbar_arrive(goA); mbar_arrive(goB); }
     };
     // per-tile state of this thread's row
-    struct TileCtx { uint32_t q, ray_first; int nrays, ri; bool valid; const float *frow; float x[3], u; };
+    struct TileCtx { uint32_t q, ray_first; int nrays, ri; bool valid; const unsigned char *rec; };
     const uint32_t Nu = (uint32_t)N, Su = (uint32_t)S;
     auto open_tile = [&](long long tile, TileCtx &c) {
       const uint32_t q0 = (uint32_t)tile * 128u;
@@ -400,77 +485,33 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
       const uint32_t q_last = q0 + 127u < Nu ? q0 + 127u : Nu - 1u;
       c.nrays = (int)(q_last / Su - c.ray_first) + 1;
       c.ri = c.valid ? (int)(c.q / Su - c.ray_first) : 0;
-      c.frow = feat + tile * f_tile_stride + (long long)row * f_row_stride;
+      c.rec = oper + tile * rec_bytes + row * 16;                 // this row's 16 bytes of chunk 0 of the tile's record
     };
-    // ---- staging of a tile's narrow operands in the slot's 64 KB -----------------------------------------------------
-    // warpgroup 0: PE(ndc) -> chunks 0..7 (hi) / 8..15 (lo), and the same 64 words to this slot's global stash (L2):
-    // round 5 reloads them as the TMEM operand of the skip connection instead of recomputing 6 sincos + 54 double angles
-    uint4 *stash = pe_stash + ((size_t)blockIdx.x * 2 + s) * 16 * 128 + row;        // word group j at stash[j * 128]
-    auto load_xu = [&](TileCtx &c) {
-      if (c.valid) { c.x[0] = __ldg(ndc_pts + 3 * c.q); c.x[1] = __ldg(ndc_pts + 3 * c.q + 1); c.x[2] = __ldg(ndc_pts + 3 * c.q + 2); }
-      else { c.x[0] = c.x[1] = c.x[2] = 0.f; }
-      c.u = 1.0f - (c.valid ? __ldg(c.frow + (F - 1) * f_k_stride) : 0.0f);          // models.py:149
-    };
-    auto stage_pe = [&](const TileCtx &c) {
-      float pe[64];
-      pos_enc<10>(c.x, pe);
-      pe[63] = 0.0f;
+    // [img feats | 1]: K2's hi / lo chunks, 4 chunks (32 channels) per batch, parked in the idle half of P (columns 64.. hi
+    // words, 96.. lo words) until `mod` is dead
+    auto park_imgf = [&](const TileCtx &c, int b) {
+      uint32_t wh[16], wl[16];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        uint32_t hi[4], lo[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) split2(pe[8 * k + 2 * i], pe[8 * k + 2 * i + 1], hi[i], lo[i]);
-        sts128(mod_row + k * CHUNK, hi[0], hi[1], hi[2], hi[3]);
-        sts128(mod_row + LOD + k * CHUNK, lo[0], lo[1], lo[2], lo[3]);
-        stash[k * 128] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-        stash[(8 + k) * 128] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      for (int k = 0; k < 4; ++k) {
+        uint4 h4 = make_uint4(0, 0, 0, 0), l4 = h4;
+        if (4 * b + k < Kb8) {
+          h4 = __ldg(reinterpret_cast<const uint4 *>(c.rec + (size_t)(2 * Kf8 + 4 * b + k) * 2048));
+          l4 = __ldg(reinterpret_cast<const uint4 *>(c.rec + (size_t)(2 * Kf8 + Kb8 + 4 * b + k) * 2048));
+        }
+        wh[4 * k] = h4.x; wh[4 * k + 1] = h4.y; wh[4 * k + 2] = h4.z; wh[4 * k + 3] = h4.w;
+        wl[4 * k] = l4.x; wl[4 * k + 1] = l4.y; wl[4 * k + 2] = l4.z; wl[4 * k + 3] = l4.w;
       }
-    };
-    // warpgroup 1: [film inputs | 1] -> chunks 16.. (hi) / 24.. (lo), 32 channels (4 chunks) per batch; a batch is LOADED
-    // at the end of one epilogue step and STORED at the start of the next, so its latency hides behind an accumulator wait
-    float fin[32];
-    auto load_film = [&](const TileCtx &c, int g4) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const int k = 8 * g4 + i;
-        fin[i] = (k < Kfilm_real && c.valid) ? __ldg(c.frow + k * f_k_stride) : (k == Kfilm_real ? 1.0f : 0.0f);
-      }
-    };
-    auto store_film = [&](int g4) {
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (g4 + k < L.Kfilm / 8) store_chunk_ss(mod_row, 16 + g4 + k, fin + 8 * k);
-    };
-    // [img feats | 1], 32 channels per batch, parked as bf16 hi/lo words in the idle half of P (columns 64.. hi, 96.. lo)
-    auto load_imgf = [&](const TileCtx &c, int b) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const int k = 32 * b + i;
-        fin[i] = (k < Kfb_real && c.valid) ? __ldg(c.frow + (Kfilm_real + k) * f_k_stride) : (k == Kfb_real ? 1.0f : 0.0f);
-      }
-    };
-    auto park_imgf = [&](int b) {
-      uint32_t hi[16], lo[16];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) split2(fin[2 * i], fin[2 * i + 1], hi[i], lo[i]);
-      tmem_st16(t_P + 64 + 16 * b, hi);
-      tmem_st16(t_P + 96 + 16 * b, lo);
+      tmem_st16(t_P + 64 + 16 * b, wh);
+      tmem_st16(t_P + 96 + 16 * b, wl);
     };
 
-    TileCtx cur, nxt;
+    TileCtx cur;
     long long tile = 2ll * blockIdx.x + s;
-    if (tile < ntiles) {
+    if (tile < ntiles) arrive_both(false);                       // round 0 of the first tile: P and Q are free
+    for (int kt = 0; tile < ntiles; tile += 2ll * gridDim.x, ++kt) {
+      const bool has_next = tile + 2ll * gridDim.x < ntiles;
+      const int par = kt & 1;                                    // parity of the stager's double buffers (stash, ubuf)
       open_tile(tile, cur);
-      if (hf == 0) { load_xu(cur); stage_pe(cur); }
-      else {
-#pragma unroll 1
-        for (int g4 = 0; g4 < L.Kfilm / 8; g4 += 4) { load_film(cur, g4); store_film(g4); }
-      }
-      arrive_both(true);
-    }
-    for (; tile < ntiles; tile += 2ll * gridDim.x) {
-      const long long ntile = tile + 2ll * gridDim.x;
-      const bool has_next = ntile < ntiles;
 #pragma unroll 1
       for (int r = 0; r < NROUND; ++r) {
         mbar_wait_backoff(my_acc, ph_acc);
@@ -500,6 +541,9 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
           if (hf == 0) {                                         // skip connection: PE words back as TMEM operand units 0..3 of P
             uint4 sw[16];
 #pragma unroll
+            u_cur = ubuf_s[(s * 2 + par) * 128 + row];           // (the stager reuses this buffer once round 7 is done)
+            const uint4 *stash = pe_stash + (((size_t)blockIdx.x * 2 + s) * 2 + par) * 16 * 128 + row;
+#pragma unroll
             for (int j = 0; j < 16; ++j) sw[j] = __ldcg(stash + j * 128);
 #pragma unroll
             for (int u4 = 0; u4 < 4; ++u4) {
@@ -520,13 +564,15 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
               cp_async16(smem_u32(rayb_s + (s * rpt + i) * 128 + (row & 31) * 4),
                          rayterm + (size_t)(cur.ray_first + i) * 128 + (row & 31) * 4);
             cp_async_commit();
-            load_imgf(cur, 0); park_imgf(0);
-            if (Kfb_real >= 32) { load_imgf(cur, 1); park_imgf(1); }
+            park_imgf(cur, 0);
+            if (Kb8 > 4) park_imgf(cur, 1);
             tmem_wait_st();                                      // read back by this thread in round 6
           }
         } else if (r == 6) {
           head[0] = head[1] = head[2] = head[3] = 0.f;
           EPI_PAIR(0, true, t_Q, 0, bias_s + 128 * 5, nullptr, hw.base, false);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_modfree + 8 * s);       // this warp's last `mod` read of the tile: chunks 16.. may be restaged
           // [img feats | 1] from their parking columns (written by this very thread in round 5) to the shared-memory A
           // operand of fb, hi words -> chunks 0.., lo words -> chunks 8..: those column groups are `mod` of both
           // warpgroups, so warpgroup 1 moves them once both have finished their last FiLM epilogue of the tile
@@ -557,27 +603,17 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
             base4[0] = head[0] + o.x + bb[0]; base4[1] = head[1] + o.y + bb[1];
             base4[2] = head[2] + o.z + bb[2]; base4[3] = head[3] + o.w + bb[3];
           }
-          if (has_next) {
-            // next tile's operands, spread over the tails of rounds 6 and 7 (a global load issued under this traffic
-            // takes 2-3 K cycles): the slot's chunks 16.. are free now (fb reads chunks 0..15 only)
-            open_tile(ntile, nxt);
-            if (hf == 0) load_xu(nxt); else { load_film(nxt, 0); store_film(0); }
-          }
         } else if (r == 7) {
           EPI_LOOP(3, t_P, t_Q, nullptr, false);
           arrive_both(false);
-          if (has_next) {                                        // fb's MMAs are done: chunks 0..15 are free too
-            if (hf == 0) stage_pe(nxt);                          // overlaps round 8's MMAs
-            else if (L.Kfilm > 32) { load_film(nxt, 4); store_film(4); }
-          }
         } else if (r == 8) {
           if (hf == 1) cp_async_wait_all();                      // per-ray terms landed (ordered before round 9 by the go barrier)
           const float *bf = f32s + ucn::X3Layout::b_feat;
           EPI_LOOP(1, t_Q, 0, bf, true);
         } else {
-          // round 9's MMAs are complete: Q is free and the next tile's operands are staged -> its film MMAs may start
-          // (go 0,1); its L0 MMAs overwrite P and wait for this epilogue's reads (go 2,3)
-          if (has_next) { fence_async_smem(); __syncwarp(); if (lane == 0) mbar_arrive(goA); }
+          // round 9's MMAs are complete: Q is free -> the next tile's film MMAs may start (go 0,1, once the stager warps
+          // have placed its operands); its L0 MMAs overwrite P and wait for this epilogue's reads (go 2,3)
+          if (has_next) { __syncwarp(); if (lane == 0) mbar_arrive(goA); }
           head[0] = head[1] = head[2] = head[3] = 0.f;
           const float *rb = rayb_s + (s * rpt + cur.ri) * 128;
           EPI_PAIR(2, true, t_P, 0, f32s + ucn::X3Layout::b_vv, rb, hw.adapt, false);
@@ -590,7 +626,7 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
             const float4 o = exch_s[s * 128 + row];
             const float *bb = f32s + ucn::X3Layout::b_adapt;
             const float ad[4] = {head[0] + o.x + bb[0], head[1] + o.y + bb[1], head[2] + o.z + bb[2], head[3] + o.w + bb[3]};
-            const float u = cur.u, cf = 1.0f - u;                // models.py:177-180
+            const float u = u_cur, cf = 1.0f - u;                // models.py:177-180
             float4 out;
             out.x = 1.0f / (1.0f + __expf(-(base4[0] * cf + ad[0] * u)));
             out.y = 1.0f / (1.0f + __expf(-(base4[1] * cf + ad[1] * u)));
@@ -601,7 +637,6 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
         }
         tr.ev(4, r, g);
       }
-      if (has_next) cur = nxt;
     }
   }
   tc_fence_before();
@@ -662,7 +697,8 @@ static int make_plan_p(int V, int S, Plan &P) {
     P.off_f32 = o;  o += (ucn::X3Layout::kSmemFloats * 4 + 127) & ~127u;
     P.off_exch = o; o += 2 * 128 * 16;
     P.off_rayb = o; o += 2u * rpt * 128 * 4;
-    P.off_bars = o; o += (8 + 2 + 2 * nst) * 8 + 16;
+    P.off_ubuf = o; o += 2u * 2 * 128 * 4;
+    P.off_bars = o; o += (8 + 2 + 2 * nst + 6) * 8 + 16;
     P.smem_total = o;
     P.nst = (uint8_t)nst;
     if (o <= 232448u - 1024u) return 0;              // 1 KB of static shared memory (block tables)
@@ -722,10 +758,10 @@ static void *scratch_for(void *stream, int tag, size_t bytes) {
   return p;
 }
 
-// Scratch for the PE words a slot parks between its tile's round 0 and round 5 (32 KB per slot, 64 KB per CTA; written and
-// read back by the same thread, it lives in L2).  One buffer per (device, stream): launches on one stream are ordered.
+// Scratch for the PE words of a tile (stager warps -> round 0's shared-memory operand and round 5's TMEM operand): 32 KB
+// per tile, double buffered per slot, 128 KB per CTA; it lives in L2.  One buffer per (device, stream): launches on one stream are ordered.
 static uint4 *pe_stash_for(void *stream, unsigned blocks) {
-  return static_cast<uint4 *>(scratch_for(stream, 0, (size_t)blocks * 2 * 16 * 128 * sizeof(uint4)));
+  return static_cast<uint4 *>(scratch_for(stream, 0, (size_t)blocks * 2 * 2 * 16 * 128 * sizeof(uint4)));   // [cta][slot][parity]
 }
 
 extern "C" int ucn_debug_set_flags_p(int flags) {
@@ -737,9 +773,8 @@ extern "C" int ucn_debug_set_trace_p(long long *buf) {
   return e == cudaSuccess ? UCN_OK : ucn_cuda_status(e, "ucn_debug_set_trace_p");
 }
 
-int ucn_mlp_forward_x3p(const ucn_weights *w, const float *ndc_pts, const float *feat, long long f_tile_stride,
-                        long long f_k_stride, long long f_row_stride, const float *angle, int R, int S, float *raw,
-                        void *stream) {
+int ucn_mlp_forward_x3p(const ucn_weights *w, const float *ndc_pts, const void *operand_tiles, const float *angle, int R,
+                        int S, float *raw, void *stream) {
   UCN_CHECK_ARG(w->bf16x3, "ucn_mlp_forward: split-bf16 weight pack missing");
   UCN_CHECK_ARG(w->V <= 7, "ucn_mlp_forward: tensor-core modes support at most 7 source views");
   Plan P;
@@ -772,8 +807,8 @@ int ucn_mlp_forward_x3p(const ucn_weights *w, const float *ndc_pts, const float 
     ucn_headw_store(w->bf16x3, hw.base);
   }
   mlp_x3p_kernel<<<blocks, kThreads, P.smem_total, (cudaStream_t)stream>>>(
-      P, hw, reinterpret_cast<const unsigned char *>(w->bf16x3), w->V, ndc_pts, feat, f_tile_stride, f_k_stride,
-      f_row_stride, rayterm, N, S, raw, stash);
+      P, hw, reinterpret_cast<const unsigned char *>(w->bf16x3), w->V, ndc_pts,
+      static_cast<const unsigned char *>(operand_tiles), (long long)ucn_operand_tile_bytes(w->V), rayterm, N, S, raw, stash);
   UCN_LAUNCH_CHECK("mlp_x3p_kernel");
   return UCN_OK;
 }

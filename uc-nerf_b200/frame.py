@@ -347,7 +347,8 @@ class FrameRenderer:
         S, F = self.frame.c.S, self.frame.F
         out, o = [], 0
         n_tiles = (m * S + 127) // 128
-        for shape in ((m, S), (m, 3), (m, 3), (m, S, 3), (n_tiles, F, 128), (m, S, 4)):
+        tile_floats = max(F * 128, int(self.lib.ucn_operand_tile_bytes(self.frame.c.V)) // 4)   # either interchange layout
+        for shape in ((m, S), (m, 3), (m, 3), (m, S, 3), (n_tiles, tile_floats), (m, S, 4)):
             nbytes = 4 * int(np.prod(shape))
             out.append(self.ws[o:o + nbytes].view(torch.float32).view(*shape))
             o += (nbytes + 255) & ~255
@@ -368,9 +369,13 @@ class FrameRenderer:
         timed("raygen", lambda: L.check(lib.ucn_raygen_sample(C.byref(f.c), None, ray0, m, L.ptr(f.t_vals), L.ptr(t_rand),
                                                               int(seed), L.ptr(z), L.ptr(rays_d), None, None, st), "K1"))
         timed("dir", lambda: L.check(lib.ucn_dir_feature(C.byref(f.c), L.ptr(rays_d), m, ray0, L.ptr(angle), st), "dir"))
-        tiled = self.mode == L.MLP_BF16X3_TC          # same choice as ucn_render_rays
-        gather, mlp = ((lib.ucn_gather_tiles_from_z, lib.ucn_mlp_forward_tiles) if tiled
-                       else (lib.ucn_gather_from_z, lib.ucn_mlp_forward))
+        tiled = self.mode == L.MLP_BF16X3_TC          # same choices as ucn_render_rays
+        if tiled and lib.ucn_mlp_x3_variant(0) == 2 and f.c.V <= 7:
+            gather, mlp = lib.ucn_gather_operands_from_z, lib.ucn_mlp_forward_operands
+        elif tiled:
+            gather, mlp = lib.ucn_gather_tiles_from_z, lib.ucn_mlp_forward_tiles
+        else:
+            gather, mlp = lib.ucn_gather_from_z, lib.ucn_mlp_forward
         timed("gather", lambda: L.check(gather(C.byref(f.c), L.ptr(z), None, ray0, m, L.ptr(feat), L.ptr(ndc), st), "K2"))
         timed("mlp", lambda: L.check(mlp(C.byref(self.weights.c), L.ptr(ndc), L.ptr(feat), L.ptr(angle),
                                          m, f.c.S, L.ptr(raw), self.mode, st), "K3"))

@@ -69,6 +69,10 @@ _SIGS = {
     "ucn_gather_from_z": (C.c_int, [C.POINTER(Frame), _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp]),
     "ucn_gather_tiles_from_z": (C.c_int, [C.POINTER(Frame), _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp]),
     "ucn_mlp_forward_tiles": (C.c_int, [C.POINTER(Weights), _fp, _fp, _fp, C.c_int, C.c_int, _fp, C.c_int, _fp]),
+    "ucn_operand_tile_bytes": (C.c_size_t, [C.c_int]),
+    "ucn_gather_operands_from_z": (C.c_int, [C.POINTER(Frame), _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp]),
+    "ucn_mlp_forward_operands": (C.c_int, [C.POINTER(Weights), _fp, _fp, _fp, C.c_int, C.c_int, _fp, C.c_int, _fp]),
+    "ucn_mlp_x3_variant": (C.c_int, [C.c_int]),
     "ucn_dir_feature": (C.c_int, [C.POINTER(Frame), _fp, C.c_int, C.c_int, _fp, _fp]),
     "ucn_mlp_forward": (C.c_int, [C.POINTER(Weights), _fp, _fp, _fp, C.c_int, C.c_int, _fp, C.c_int, _fp]),
     "ucn_composite": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp, _fp]),
