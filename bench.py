@@ -337,7 +337,8 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
         comp_gbs = (20 * S + 16) * n_tile / (kern["composite"] * 1e-3) / 1e9
         ray_gbs = (4 * S + 36) * n_tile / (kern["raygen"] * 1e-3) / 1e9
         total_rays = n_frame * (world if (replicas and world > 1) else 1)
-        kname = {"bf16": "mlp_x3_kernel", "bf16_fast": "mlp_tc_kernel", "fp32": "mlp_fp32_kernel"}[args.mode]
+        x3 = "mlp_x3p_kernel" if L.load().ucn_mlp_x3_variant(0) == 2 and V <= 7 else "mlp_x3_kernel"
+        kname = {"bf16": x3, "bf16_fast": "mlp_tc_kernel", "fp32": "mlp_fp32_kernel"}[args.mode]
         if split:
             par = (f"one frame as {world} contiguous row tiles (shard.row_tile), "
                    + ("K4 peer-stores each tile into the root's frame buffer over NVLink (16 B/ray), one 4-byte all-reduce per "

@@ -190,9 +190,10 @@ int ucn_mlp_forward_tiles(const ucn_weights *w, const float *ndc_pts, const floa
                           int R, int S, float *raw, int mode, void *stream);
 /* Operand tiles: the interchange format between K2 and the tensor-core MLP (UCN_MLP_BF16X3_TC).  One record of
  * ucn_operand_tile_bytes(V) bytes per 128-sample tile: [film hi | film lo | img hi | img lo] K-chunks of 128 rows x 8 bf16
- * (hi = bf16(x), lo = bf16(x - hi); film = mvs feats 24 | (r,g,b,mask) x V | 1 | 0.., img = image feats 8 x V | 1 | 0..,
- * network/models.py:143-150) followed by the 128 sampled confidences (fp32).  A chunk is already the UMMA K-major
- * core-matrix layout, so K3 copies it into shared memory / tensor memory verbatim.  V <= 7. */
+ * (hi = bf16(x), lo = bf16(x - hi); film = mvs feats 24 | (r,g,b,mask) x V | 1 when V is odd: 3 + ceil(V/2) chunks,
+ * img = image feats 8 x V: V chunks; network/models.py:143-150) followed by the 128 sampled confidences (fp32).  Chunks
+ * that would hold only the bias ones column or zero K padding are not stored (K3 writes those constants).  A chunk is
+ * already the UMMA K-major core-matrix layout, so K3 copies it into shared memory / tensor memory verbatim.  V <= 7. */
 size_t ucn_operand_tile_bytes(int V);
 /* K2 writing operand tiles (same gathers as ucn_gather_tiles_from_z; network/renderer.py:177-212) */
 int ucn_gather_operands_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R,

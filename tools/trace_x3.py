@@ -19,17 +19,18 @@ feat[:, -1, :] = torch.rand((NT, 128), device="cuda", generator=g)
 if not V1:
     # operand tiles of the same rows (ucn_gather.cu): [film hi | film lo | img hi | img lo] chunks of [128][8] bf16 + confidence
     kf, kb = 24 + 4 * V, 8 * V
-    Kf, Kb = (kf + 1 + 15) // 16 * 16, (kb + 1 + 15) // 16 * 16
-    def chunks(x, K):                                                 # x [NT, k, 128] fp32 -> hi, lo [NT, K/8, 128, 8] bf16
-        pad = torch.zeros((NT, K, 128), device="cuda")
+    cf, cb = 3 + (V + 1) // 2, V                                      # stored chunks per half
+    def chunks(x, n_chunks, ones):                                    # x [NT, k, 128] fp32 -> hi, lo [NT, chunks, 128, 8] bf16
+        pad = torch.zeros((NT, 8 * n_chunks, 128), device="cuda")
         pad[:, :x.shape[1]] = x
-        pad[:, x.shape[1]] = 1.0
+        if ones:
+            pad[:, x.shape[1]] = 1.0
         hi = pad.to(torch.bfloat16)
         lo = (pad - hi.float()).to(torch.bfloat16)
-        f = lambda t: t.view(NT, K // 8, 8, 128).permute(0, 1, 3, 2).contiguous()
+        f = lambda t: t.view(NT, n_chunks, 8, 128).permute(0, 1, 3, 2).contiguous()
         return f(hi), f(lo)
-    fh, fl = chunks(feat[:, :kf], Kf)
-    ih, il = chunks(feat[:, kf:kf + kb], Kb)
+    fh, fl = chunks(feat[:, :kf], cf, V % 2 == 1)
+    ih, il = chunks(feat[:, kf:kf + kb], cb, False)
     rec = torch.cat([t.view(torch.uint8).reshape(NT, -1) for t in (fh, fl, ih, il)] +
                     [feat[:, -1, :].contiguous().view(torch.uint8).reshape(NT, -1)], dim=1).contiguous()
     assert rec.shape[1] == lib.ucn_operand_tile_bytes(V)

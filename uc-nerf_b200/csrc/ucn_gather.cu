@@ -64,16 +64,16 @@ __device__ __forceinline__ Acc8 tri8(const float *__restrict__ vol, int D, int h
 
 // ---- operand tiles (OUT = 2): what the tensor-core MLP's shared-memory / TMEM operands are made of -----------------
 // One 128-sample tile = one record of ucn_operand_tile_bytes(V) bytes:
-//   film hi | film lo   Kfilm/8 chunks each: [mvs feats 24 | (r,g,b,mask) x V | 1 | 0...]   (models.py:143-150)
-//   img  hi | img  lo   Kfb/8 chunks each:   [img feats 8 x V | 1 | 0...]                  (models.py:147)
-//   confidence          128 fp32                                                            (models.py:149)
+//   film hi | film lo   3 + ceil(V/2) chunks each: [mvs feats 24 | (r,g,b,mask) x V | 1 (V odd)]   (models.py:143-150)
+//   img  hi | img  lo   V chunks each:             [img feats 8 x V]                              (models.py:147)
+//   confidence          128 fp32                                                                   (models.py:149)
+// Only chunks that carry data are stored: the chunk that holds nothing but the ones column (V even: film; always: img) and
+// the all-zero K padding up to a multiple of 16 are constants K3 writes itself.
 // a chunk = 8 consecutive K values of the 128 rows as bf16, [row][8] (2 KB) -- the UMMA no-swizzle K-major core-matrix
 // layout, so K3 copies chunks verbatim (cp.async / 128-bit loads); hi = bf16(x), lo = bf16(x - hi), the split K3's
 // round-1 kernel did itself.  The "1" is the ones column that folds the layer's bias into the MMA.
-struct OperGeom { int kf8, kb8; };
-__device__ __forceinline__ OperGeom oper_geom(int V) {
-  return {((24 + 4 * V + 1 + 15) & ~15) / 8, ((8 * V + 1 + 15) & ~15) / 8};
-}
+struct OperGeom { int kf8, kb8; };                         // stored (data) chunks per half
+__host__ __device__ __forceinline__ OperGeom oper_geom(int V) { return {3 + (V + 1) / 2, V}; }
 __device__ __forceinline__ uint32_t bf2(float lo, float hi) {
   uint32_t r;
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
@@ -218,11 +218,7 @@ gather_kernel(const __grid_constant__ ucn_frame f, const float *__restrict__ pts
       if (V & 1) {                                           // last view sits in the low half of its chunk; the 1 follows it
         tail[0] = cbuf[0]; tail[1] = cbuf[1]; tail[2] = cbuf[2]; tail[3] = cbuf[3]; tail[4] = 1.0f;
       } else tail[0] = 1.0f;
-      emit_chunk(film_hi, film_lo, kc, tail);
-      for (++kc; kc < og.kf8; ++kc) emit_chunk(film_hi, film_lo, kc, zero8);
-      const float one8[8] = {1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      emit_chunk(img_hi, img_lo, V, one8);
-      for (kc = V + 1; kc < og.kb8; ++kc) emit_chunk(img_hi, img_lo, kc, zero8);
+      if (V & 1) emit_chunk(film_hi, film_lo, kc, tail);     // (V even: the ones column is a chunk of its own -- not stored)
     } else {
       for (int kc = 0; kc < og.kf8; ++kc) emit_chunk(film_hi, film_lo, kc, zero8);
       for (int kc = 0; kc < og.kb8; ++kc) emit_chunk(img_hi, img_lo, kc, zero8);
@@ -305,8 +301,8 @@ extern "C" int ucn_gather_tiles_from_z(const ucn_frame *f, const float *z, const
 }
 
 extern "C" size_t ucn_operand_tile_bytes(int V) {
-  const int kf8 = ((24 + 4 * V + 1 + 15) & ~15) / 8, kb8 = ((8 * V + 1 + 15) & ~15) / 8;
-  return (size_t)(2 * kf8 + 2 * kb8) * 2048 + 512;
+  const OperGeom og = oper_geom(V);
+  return (size_t)(2 * og.kf8 + 2 * og.kb8) * 2048 + 512;
 }
 
 extern "C" int ucn_gather_operands_from_z(const ucn_frame *f, const float *z, const float *pix_yx, int ray0, int R,

@@ -245,7 +245,9 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
   float4 *exch_s = reinterpret_cast<float4 *>(smem + plan.off_exch);
   float *rayb_s = reinterpret_cast<float *>(smem + plan.off_rayb);
   __shared__ uint32_t blk_s[MAXBLK], goff_s[MAXBLK];
-  const int Kf8 = L.Kfilm / 8, Kb8 = L.Kfb / 8;               // K-chunks of the film / img operands (ucn_gather.cu: operand tiles)
+  // K-chunks of the film / img operands, and how many of them K2's operand tile stores (ucn_gather.cu): the rest -- the
+  // chunk that is only the ones column (bias), and zero K padding -- are constants written here
+  const int Kf8 = L.Kfilm / 8, Kb8 = L.Kfb / 8, Kfd = 3 + (V + 1) / 2, Kbd = V;
   const float *f32g = reinterpret_cast<const float *>(wpack + L.f32);
 
   // ---- one-time setup ---------------------------------------------------------------------------
@@ -393,7 +395,7 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
           const bool valid = q < Nu;
           float x[3] = {0.f, 0.f, 0.f};
           if (valid) { x[0] = __ldg(ndc_pts + 3 * q); x[1] = __ldg(ndc_pts + 3 * q + 1); x[2] = __ldg(ndc_pts + 3 * q + 2); }
-          const float *conf = reinterpret_cast<const float *>(oper + (t0 + sl) * rec_bytes + (size_t)(2 * Kf8 + 2 * Kb8) * 2048);
+          const float *conf = reinterpret_cast<const float *>(oper + (t0 + sl) * rec_bytes + (size_t)(2 * Kfd + 2 * Kbd) * 2048);
           ubuf_s[(sl * 2 + par) * 128 + row] = 1.0f - __ldg(conf + row);                                     // models.py:149
           float pe[64];
           pos_enc<10>(x, pe);
@@ -419,8 +421,13 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
           const unsigned char *rec = oper + (t0 + sl) * rec_bytes + row * 16;
 #pragma unroll 1
           for (int c = 0; c < Kf8; ++c) {
-            cp_async16(mod_s + (16 + c) * CHUNK + row * 16, rec + (size_t)c * 2048);
-            cp_async16(mod_s + (24 + c) * CHUNK + row * 16, rec + (size_t)(Kf8 + c) * 2048);
+            if (c < Kfd) {
+              cp_async16(mod_s + (16 + c) * CHUNK + row * 16, rec + (size_t)c * 2048);
+              cp_async16(mod_s + (24 + c) * CHUNK + row * 16, rec + (size_t)(Kfd + c) * 2048);
+            } else {                                               // ones column alone (V even) / zero padding
+              sts128(mod_s + (16 + c) * CHUNK + row * 16, (c == Kfd && !(V & 1)) ? 0x3F80u : 0u, 0u, 0u, 0u);
+              sts128(mod_s + (24 + c) * CHUNK + row * 16, 0u, 0u, 0u, 0u);
+            }
           }
         }
         cp_async_commit();
@@ -494,10 +501,10 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         uint4 h4 = make_uint4(0, 0, 0, 0), l4 = h4;
-        if (4 * b + k < Kb8) {
-          h4 = __ldg(reinterpret_cast<const uint4 *>(c.rec + (size_t)(2 * Kf8 + 4 * b + k) * 2048));
-          l4 = __ldg(reinterpret_cast<const uint4 *>(c.rec + (size_t)(2 * Kf8 + Kb8 + 4 * b + k) * 2048));
-        }
+        if (4 * b + k < Kbd) {
+          h4 = __ldg(reinterpret_cast<const uint4 *>(c.rec + (size_t)(2 * Kfd + 4 * b + k) * 2048));
+          l4 = __ldg(reinterpret_cast<const uint4 *>(c.rec + (size_t)(2 * Kfd + Kbd + 4 * b + k) * 2048));
+        } else if (4 * b + k == Kbd) h4.x = 0x3F80u;               // the ones column (bias of pts_bias_confidence): bf16 1.0
         wh[4 * k] = h4.x; wh[4 * k + 1] = h4.y; wh[4 * k + 2] = h4.z; wh[4 * k + 3] = h4.w;
         wl[4 * k] = l4.x; wl[4 * k + 1] = l4.y; wl[4 * k + 2] = l4.z; wl[4 * k + 3] = l4.w;
       }
