@@ -37,7 +37,7 @@ raygen_sample_kernel(const __grid_constant__ ucn_frame f, const float *__restric
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = blockIdx.x * kWarpsPerBlock + warp;
   if (r >= R) return;
-  float *zs = smem + (size_t)warp * P;
+  float *zs = smem + (size_t)warp * 2 * P;                       // [P] sorted candidates | [P] the three sweeps
   const int S = f.S, n = S / 3;
 
   float ys, xs;
@@ -46,35 +46,43 @@ raygen_sample_kernel(const __grid_constant__ ucn_frame f, const float *__restric
   ucn::ray_dir(f, ys, xs, d);
   ucn::stage_near_far(f, ys, xs, nr, fr);
 
-  // three uniform sweeps, near*(1-t) + far*t with separate roundings (utils/utils.py:396)
+  // three uniform sweeps, near*(1-t) + far*t with separate roundings (utils/utils.py:396), computed ONCE into shared
+  // memory (sw[k*n + j]): the rank-merge below probes them ~12 times per element, and a probe is then one LDS instead of
+  // a t_vals load + 5 roundings + selects
+  float *sw = zs + P;
   auto sweep = [&](int k, int j) {           // (selects, not indexing: nr/fr stay in registers)
     const float t = __ldg(t_vals + j);
     const float nk = k == 0 ? nr[0] : (k == 1 ? nr[1] : nr[2]), fk = k == 0 ? fr[0] : (k == 1 ? fr[1] : fr[2]);
     return __fadd_rn(__fmul_rn(nk, __fsub_rn(1.0f, t)), __fmul_rn(fk, t));
   };
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+    for (int j = lane; j < n; j += 32) sw[k * n + j] = sweep(k, j);
+  __syncwarp();
   // torch.sort of their concatenation (utils/utils.py:698-700), values only.  Each sweep is non-decreasing (checked
   // below), so the sorted position of element j of sweep k is j + the number of smaller elements in the other two
-  // sweeps: two 6-step binary searches per element instead of a 28-stage bitonic network.  Ties between sweeps are
+  // sweeps: two binary searches per element instead of a 28-stage bitonic network.  Ties between sweeps are
   // broken by sweep index (<= against earlier sweeps, < against later ones), which makes the ranks a permutation;
   // equal values are interchangeable in a value-only sort.
   bool monotone = true;
-  for (int i = lane; i < S; i += 32) {
-    const int k = i / n, j = i - k * n;
-    if (j + 1 < n) monotone = monotone && (sweep(k, j) <= sweep(k, j + 1));
-  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+    for (int j = lane; j + 1 < n; j += 32) monotone = monotone && (sw[k * n + j] <= sw[k * n + j + 1]);
   if (__all_sync(0xffffffffu, monotone)) {
-    for (int i = lane; i < S; i += 32) {
-      const int k = i / n, j = i - k * n;
-      const float v = sweep(k, j);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+    for (int j = lane; j < n; j += 32) {
+      const float v = sw[k * n + j];
       int rank = j;
 #pragma unroll
       for (int m = 0; m < 3; ++m) {
         if (m == k) continue;
         // number of elements of sweep m that sort before v: first index with sweep(m, idx) > v (m < k) or >= v (m > k)
+        const float *sm = sw + m * n;
         int lo = 0, hi = n;
         while (lo < hi) {
           const int mid = (lo + hi) >> 1;
-          const float w = sweep(m, mid);
+          const float w = sm[mid];
           const bool before = m < k ? (w <= v) : (w < v);
           if (before) lo = mid + 1; else hi = mid;
         }
@@ -114,19 +122,23 @@ raygen_sample_kernel(const __grid_constant__ ucn_frame f, const float *__restric
   const float iw = (float)(f.W - 1), ih = (float)(f.H - 1);
   const size_t plane = (size_t)R * S * 3;
   const int g = pix_yx ? r : ray0 + r;                         // RNG counter: global ray id
-  for (int i = lane; i < S; i += 32) {
+  // a lane owns 4 consecutive samples: ONE Philox4x32-10 call (counter = sample / 4) yields their 4 uniforms -- the same
+  // uniform per (ray, sample) as a call per sample, a quarter of the integer multiplies
+  for (int i4 = 4 * lane; i4 < S; i4 += 128) {
+    uint32_t w4[4] = {0u, 0u, 0u, 0u};
+    if (!t_rand) {
+      const uint4 rnd = philox4x32(make_uint4((uint32_t)g, (uint32_t)(i4 >> 2), 0u, 0u),
+                                   make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+      w4[0] = rnd.x; w4[1] = rnd.y; w4[2] = rnd.z; w4[3] = rnd.w;
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+    const int i = i4 + e;
+    if (i >= S) break;
     const float zc = zs[i];
     const float lower = i == 0 ? zc : __fmul_rn(0.5f, __fadd_rn(zc, zs[i - 1]));
     const float upper = i == S - 1 ? zc : __fmul_rn(0.5f, __fadd_rn(zs[i + 1], zc));
-    float u;
-    if (t_rand) {
-      u = __ldg(t_rand + (size_t)r * S + i);
-    } else {
-      const uint4 rnd = philox4x32(make_uint4((uint32_t)g, (uint32_t)(i >> 2), 0u, 0u),
-                                   make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
-      const uint32_t w4[4] = {rnd.x, rnd.y, rnd.z, rnd.w};
-      u = u01(w4[i & 3]);
-    }
+    const float u = t_rand ? __ldg(t_rand + (size_t)r * S + i) : u01(w4[e]);
     const float zj = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), u));      // :706
     const size_t q = (size_t)r * S + i;
     z_out[q] = zj;
@@ -145,6 +157,7 @@ raygen_sample_kernel(const __grid_constant__ ucn_frame f, const float *__restric
           dst[2] = __fdiv_rn(__fsub_rn(pz, nn), __fsub_rn(ff, nn));
         }
       }
+    }
     }
   }
 }
@@ -213,7 +226,12 @@ extern "C" int ucn_raygen_sample(const ucn_frame *f, const float *pix_yx, int ra
   if (R == 0) return UCN_OK;
   int P = 32;
   while (P < f->S) P <<= 1;
-  const size_t smem = (size_t)kWarpsPerBlock * P * sizeof(float);
+  const size_t smem = (size_t)kWarpsPerBlock * 2 * P * sizeof(float);
+  static int attr[kUcnMaxDevices];
+  if (smem > 48 * 1024) {
+    cudaError_t e = ucn_ensure_dyn_smem(raygen_sample_kernel, (int)smem, attr);
+    if (e != cudaSuccess) return ucn_cuda_status(e, "raygen smem attribute");
+  }
   const int blocks = (R + kWarpsPerBlock - 1) / kWarpsPerBlock;
   raygen_sample_kernel<<<blocks, kWarpsPerBlock * 32, smem, (cudaStream_t)stream>>>(
       *f, pix_yx, ray0, R, t_vals, t_rand, seed, P, z, rays_d, pts, ndc);
