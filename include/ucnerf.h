@@ -300,6 +300,18 @@ int ucn_depth_median(const float *gt, const float *pred, const unsigned char *ma
 int ucn_depth_errors(const float *gt, const float *pred, const unsigned char *mask, int64_t n, float min_depth,
                      float max_depth, float ratio, double *out8, void *stream);
 
+/* ---- training sampler: ray selection in one launch (utils/utils.py:450-479,169-215,217-247,274-320) ------------- */
+/* pix_yx [2][R] fp32 (row, col), R = 2*(patch_num/2)*patch_size^2 + n_rand + n_depth: patch_num/2 patches drawn by a
+ * confidence-weighted multinomial without replacement, patch_num/2 by (1 - confidence) (patch offset clamped to
+ * [0, H/ps - 2], uniform shift in [0, ps) per patch), n_rand uniform pixels (inside the centre crop when crop != 0),
+ * then the n_depth sparse-depth coordinates coords_rc [n_depth][2] int64 (row, col).  Same distribution as the
+ * reference's torch.multinomial / randint sequence (the exponential race torch runs itself), keyed by `seed`.
+ * workspace: ucn_select_workspace_bytes() bytes, zero-filled ONCE by the caller before its first use. */
+size_t ucn_select_workspace_bytes(int H, int W, int patch_num);
+int ucn_select_training_pixels(const float *confidence, int H, int W, int n_rand, int patch_num, int patch_size, int crop,
+                               const long long *coords_rc, int n_depth, uint64_t seed, void *workspace, float *pix_yx,
+                               void *stream);
+
 /* ---- multi-GPU: peer-mapped frame buffer (the reference is single-GPU, train.py:433) ------ */
 /* One process per GPU.  The root allocates the [H*W][4]-float frame buffer and exports a 64-byte CUDA IPC handle;
  * every other process opens it with its own device current and passes tile pointers inside it as ucn_render_rays'

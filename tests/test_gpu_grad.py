@@ -233,13 +233,16 @@ def test_build_rays_matches_reference_sampler(name):
                         pose_ref["intrinsics"], c["N_rays"], S, with_depth=False, outputs=outputs)
 
 
-def test_training_pixel_selection_properties():
-    """Selection stays in PyTorch: counts, bounds, patch structure, sparse-depth rays last (utils/utils.py:450-496)."""
+@pytest.mark.parametrize("fused", (True, False))
+def test_training_pixel_selection_properties(fused):
+    """Selection in one launch (ucn_select_training_pixels) and its PyTorch form (with a torch.Generator): counts, bounds,
+    patch structure, sparse-depth rays last (utils/utils.py:450-496)."""
     from ucnerf_b200 import rays
     H, W, ps, pn, N = 64, 80, 4, 10, 256
     conf = torch.rand((1, H, W), device=DEV)
     coords = torch.stack((torch.randint(0, H, (50,)), torch.randint(0, W, (50,))), 1).to(DEV)
-    pix = rays.select_training_pixels(H, W, conf, coords, N, pn, ps)
+    gen = None if fused else torch.Generator(DEV).manual_seed(5)
+    pix = rays.select_training_pixels(H, W, conf, coords, N, pn, ps, generator=gen)
     assert tuple(pix.shape) == (2, N + 50) and pix.dtype == torch.float32
     assert float(pix[0].min()) >= 0 and float(pix[0].max()) <= H - 1 and float(pix[1].min()) >= 0 and float(pix[1].max()) <= W - 1
     patches = pix[:, :pn * ps * ps].reshape(2, pn, ps, ps)
@@ -247,7 +250,40 @@ def test_training_pixel_selection_properties():
     assert torch.equal(patches[1, :, :, 1:] - patches[1, :, :, :-1], torch.ones_like(patches[1, :, :, 1:]))   # cols step by 1
     assert torch.equal(pix[:, N:].long(), coords.t())
     with pytest.raises(Exception):
-        rays.select_training_pixels(H, W, conf, coords, pn * ps * ps - 1, pn, ps)        # quirk Q20
+        rays.select_training_pixels(H, W, conf, coords, pn * ps * ps - 1, pn, ps, generator=gen)        # quirk Q20
+    if fused:                                                    # same seed -> same selection; another seed -> another one
+        a = rays.select_training_pixels(H, W, conf, coords, N, pn, ps, seed=11)
+        b = rays.select_training_pixels(H, W, conf, coords, N, pn, ps, seed=11)
+        c = rays.select_training_pixels(H, W, conf, coords, N, pn, ps, seed=12)
+        assert torch.equal(a, b) and not torch.equal(a, c)
+        crop = rays.select_training_pixels(H, W, conf, None, 4096, pn, ps, seed=3, is_precrop_iters=True)
+        assert crop.shape[1] == 4096
+
+
+def test_fused_selection_follows_the_confidence():
+    """Distribution check of the one-launch selection: with confidence concentrated on the left half of the image the
+    confidence-drawn patches land there and the (1 - confidence)-drawn patches on the right (utils/utils.py:450-468);
+    distinct pixels per draw (sampling WITHOUT replacement); uniform pixels cover the image; statistics agree with the
+    torch.multinomial form on the same map."""
+    from ucnerf_b200 import rays
+    H, W, ps, pn = 64, 96, 4, 40
+    conf = torch.full((1, H, W), 0.02, device=DEV)
+    conf[:, :, :W // 2] = 0.98
+    left_c, left_u, distinct = [], [], True
+    for seed in range(40):
+        pix = rays.select_training_pixels(H, W, conf, None, pn * ps * ps + 512, pn, ps, seed=seed)
+        firsts = pix[:, :pn * ps * ps].reshape(2, pn, ps * ps)[:, :, 0]                      # top-left pixel of every patch
+        left_c.append((firsts[1, :pn // 2] < W // 2 - ps).float().mean().item())             # drawn by confidence
+        left_u.append((firsts[1, pn // 2:] < W // 2 - ps).float().mean().item())             # drawn by 1 - confidence
+        rnd = pix[:, pn * ps * ps:]
+        assert 0 <= float(rnd[0].min()) and float(rnd[0].max()) <= H - 1 and 0 <= float(rnd[1].min()) and float(rnd[1].max()) <= W - 1
+        assert float(rnd[1].mean()) > 0.35 * W and float(rnd[1].mean()) < 0.65 * W
+    # P(confidence draw on the left) = 0.98 / (0.98 + 0.02) = 0.98; the patch offset clamp / shift moves a few across
+    assert np.mean(left_c) > 0.85 and np.mean(left_u) < 0.15, (np.mean(left_c), np.mean(left_u))
+    gen = torch.Generator(DEV).manual_seed(0)
+    ref = [rays.select_training_pixels(H, W, conf, None, pn * ps * ps + 512, pn, ps, generator=gen) for _ in range(40)]
+    ref_c = np.mean([(p[:, :pn * ps * ps].reshape(2, pn, ps * ps)[1, :pn // 2, 0] < W // 2 - ps).float().mean().item() for p in ref])
+    assert abs(ref_c - np.mean(left_c)) < 0.08, (ref_c, np.mean(left_c))
 
 
 @pytest.mark.parametrize("R,S,V", ((37, 12, 3), (1, 3, 1), (5, 126, 5), (300, 3, 2)))

@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libucnerf.so")
 SOURCES = ["ucn_api.cu", "ucn_pack.cu", "ucn_rays.cu", "ucn_gather.cu", "ucn_mlp_fp32.cu", "ucn_mlp_tc.cu", "ucn_mlp_x3.cu", "ucn_mlp_x3p.cu",
-           "ucn_composite.cu", "ucn_backward.cu", "ucn_train.cu", "ucn_metrics.cu", "ucn_costvol.cu", "ucn_losses.cu"]
+           "ucn_composite.cu", "ucn_backward.cu", "ucn_train.cu", "ucn_metrics.cu", "ucn_costvol.cu", "ucn_losses.cu", "ucn_select.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 

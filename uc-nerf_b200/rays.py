@@ -301,16 +301,39 @@ def build_color_volume(point_samples, pose_ref, imgs, near_far=None, img_feat=No
 
 # ---- training sampler -------------------------------------------------------------------
 
+_SELECT_WS: Dict[tuple, torch.Tensor] = {}
+
+
 def select_training_pixels(H, W, confidence, coords, N_rays, patch_num, patch_size, generator=None,
-                           is_precrop_iters=False):
-    """Ray SELECTION of build_rays (utils/utils.py:450-479,169-215,217-247,274-320), kept in PyTorch as the survey
-    prescribes: patch_num/2 patches drawn by confidence-multinomial, patch_num/2 by (1 - confidence), uniform random
-    pixels up to N_rays, then the sparse-depth coordinates.  The reference's per-patch Python loop is replaced by one
-    vectorised index computation (same distribution).  -> pixel_coordinates [2, R] (row, col), float32."""
+                           is_precrop_iters=False, seed: Optional[int] = None):
+    """Ray SELECTION of build_rays (utils/utils.py:450-479,169-215,217-247,274-320): patch_num/2 patches drawn by
+    confidence-multinomial, patch_num/2 by (1 - confidence), uniform random pixels up to N_rays, then the sparse-depth
+    coordinates.  -> pixel_coordinates [2, R] (row, col), float32.
+
+    One launch (`ucn_select_training_pixels`: exponential-race sampling without replacement -- what torch.multinomial
+    runs itself -- patch placement, uniform pixels and the coordinates; keyed by `seed`, default a fresh one per call).
+    With a `generator` the selection is drawn by torch instead (same distribution, ~45 small launches): the
+    reference's per-patch Python loop as one vectorised index computation, reproducible with a torch.Generator."""
     device = confidence.device
     ps, half = int(patch_size), int(patch_num) // 2
     if N_rays < 2 * half * ps * ps:
         raise L.UcnError("batch_size must be >= patch_num * patch_size^2 (utils/utils.py:468-474, quirk Q20)")
+    if generator is None and confidence.is_cuda and half <= 64 and ((H * W + 2047) // 2048) * half <= 2048:
+        lib = L.load()
+        conf = confidence.detach().reshape(-1).to(torch.float32).contiguous()
+        n_rand = int(N_rays) - 2 * half * ps * ps
+        crd = None if coords is None else coords.to(device=device, dtype=torch.int64).contiguous()
+        n_depth = 0 if crd is None else int(crd.shape[0])
+        key = (str(device), int(lib.ucn_select_workspace_bytes(H, W, int(patch_num))))
+        ws = _SELECT_WS.get(key)
+        if ws is None:
+            ws = _SELECT_WS[key] = torch.zeros(key[1], dtype=torch.uint8, device=device)
+        pix = torch.empty((2, 2 * half * ps * ps + n_rand + n_depth), device=device, dtype=torch.float32)
+        crop = int(bool(is_precrop_iters) and float(torch.rand((1,))) > 0.3)            # utils/utils.py:241
+        L.check(lib.ucn_select_training_pixels(L.ptr(conf), int(H), int(W), n_rand, int(patch_num), ps, crop, L.ptr(crd),
+                                               n_depth, int(fresh_seed() if seed is None else seed), L.ptr(ws), L.ptr(pix),
+                                               L.stream_ptr()), "ucn_select_training_pixels")
+        return pix
     conf = confidence.detach().reshape(-1).float()
     grid = torch.arange(ps, device=device)
     pix = []
