@@ -58,9 +58,11 @@ for who in range(7):
     for w, t in b[who]:
         if t: ev.append((int(t), int(w) & 0xFF, (int(w) >> 8) & 0xFF, (int(w) >> 16) & 0xFF, int(w) >> 24))
 ev.sort(); t0 = ev[0][0]
-names = {1: "mma_start", 2: "mma_issued", 3: "epi_wake", 4: "epi_done", 5: "blk_issued", 6: "point"}
+names = {1: "mma_start", 2: "mma_issued", 3: "epi_wake", 4: "epi_done", 5: "blk_issued", 6: "point", 7: "blk_waited"}
 lo, hi = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (0, 200)
 for t, tag, r, who, pay in ev[lo:hi]:
     extra = (f"  wfull_wait={pay & 0xFFFFF} go_wait={pay >> 20}" if not V1 else f"  wfull_wait={pay}") if tag == 2 else ""
+    if tag == 7:
+        extra = f"  go={pay >> 16} wfull={pay & 0xFFFF}"
     print(f"{t - t0:>8} {names[tag]:<11} r{r} {'wg' if tag in (3, 4, 6) else 'slot'}{who}{extra}")
 print("events", len(ev), "span cycles", ev[-1][0] - t0)

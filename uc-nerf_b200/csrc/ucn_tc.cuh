@@ -25,6 +25,13 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
                  : "=r"(done) : "r"(bar), "r"(parity) : "memory");
   } while (!done);
 }
+// non-blocking test of a phase (one per lane: a warp polls up to 32 barriers with one ballot)
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+               : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  return done != 0;
+}
 // long waits (epilogue warps waiting for a whole MMA round): back off between polls so the spinning warp
 // does not take issue slots from the warps that are working on the same scheduler
 __device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity) {
