@@ -236,7 +236,7 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
   const uint32_t ring = sbase + 2 * MODB;
   // barriers: go[2][4] (count 4: the warps of the warpgroup that owns the chunk), acc[2] (count 1), wfull/wempty[nst];
   // stager hand-shake per slot: modfree (count 8: every epilogue warp after its last FiLM read of the tile), r7 (count 1:
-  // fb's MMAs done, tcgen05.commit), staged (count 1: the stager warp)
+  // fb's MMAs done, tcgen05.commit), staged (count 2: both stager warps)
   const uint32_t bar_go = pin(sbase + plan.off_bars), bar_acc = pin(bar_go + 64), bar_wfull = pin(bar_acc + 16),
                  bar_wempty = pin(bar_wfull + 8 * nst), bar_modfree = pin(bar_wempty + 8 * nst), bar_r7 = pin(bar_modfree + 16),
                  bar_staged = pin(bar_r7 + 16), tmem_ptr_addr = bar_staged + 16;
@@ -254,14 +254,14 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
   for (int i = threadIdx.x; i < ucn::X3Layout::kSmemFloats; i += kThreads) f32s[i] = f32g[i];
   if (threadIdx.x < plan.nblk) {
     const Blk k = plan.blk[threadIdx.x];
-    blk_s[threadIdx.x] = (uint32_t)k.units | ((uint32_t)k.a0 << 8) | ((uint32_t)k.flags << 16) | ((uint32_t)k.wait << 24);
+    blk_s[threadIdx.x] = (uint32_t)k.units | ((uint32_t)k.a0 << 8) | ((uint32_t)k.flags << 16);
     goff_s[threadIdx.x] = k.goff;
   }
   if (threadIdx.x == 0) {
     for (int i = 0; i < 8; ++i) mbar_init(bar_go + 8 * i, 4);
     mbar_init(bar_acc, 1); mbar_init(bar_acc + 8, 1);
-    for (int i = 0; i < nst; ++i) { mbar_init(bar_wfull + 8 * i, 1); mbar_init(bar_wempty + 8 * i, 2); }   // both issuers release a stage
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_modfree + 8 * i, 8); mbar_init(bar_r7 + 8 * i, 1); mbar_init(bar_staged + 8 * i, 1); }
+    for (int i = 0; i < nst; ++i) { mbar_init(bar_wfull + 8 * i, 1); mbar_init(bar_wempty + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_modfree + 8 * i, 8); mbar_init(bar_r7 + 8 * i, 1); mbar_init(bar_staged + 8 * i, 2); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) tmem_alloc512(tmem_ptr_addr);
@@ -289,77 +289,48 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
       }
     }
     __syncwarp();
-  } else if (warp == 1 || warp == 3) {
-    // ================= MMA issuers (warp 1: slot 0, warp 3: slot 1) ================================
-    // One issuer per slot, on different SM sub-partitions: an issuer's own instruction stream (barrier tests, descriptor
-    // arithmetic in the uniform datapath, ~70 instructions per 6-MMA block, sharing its scheduler with four epilogue
-    // warps) takes 600-850 cycles per block against 400 cycles of tensor work -- a single issuer serving both slots left
-    // the tensor pipe idle a third of the time even when every barrier was complete.  The tensor pipe executes the two
-    // streams in arrival order; a weight stage is released when BOTH issuers have committed it (wempty count 2).
-    //
-    // All barriers of a round (4 go + up to 4 weight stages) are TESTED AT ONCE, one per lane, and combined with a ballot
-    // (a first version waited on each in turn: ~300 cycles per block even when everything was complete); the block table
-    // comes from shared memory; a block re-polls only while a barrier it needs is still incomplete.
-    const int s = warp == 1 ? 0 : 1;
+  } else if (warp == 1) {
+    // ================= MMA issuer =================================================================
+    // Rounds run slot 0 then slot 1 (both slots consume each weight stage, loaded once per tile pair); a block waits only
+    // for the go barriers its operands depend on (chunk j of the slot's previous epilogue for a 128-wide TMEM operand).
     const uint32_t idesc = umma_idesc_bf16(128);
     const uint64_t dt = umma_desc(0, CHUNK, 128);                 // LBO = 2048 (K-chunks of A, tiles of B), SBO = 128
     const uint32_t dhi = (uint32_t)(dt >> 32), dlo = (uint32_t)dt;
     auto mk = [&](uint32_t lo) { return ((uint64_t)dhi << 32) | lo; };
-    uint32_t st0 = 0, wph0 = 0, ph_go = 0, ph_staged = 0;
-    Tracer tr(s == 0 ? 0 : 5);
+    uint32_t st0 = 0, wph0 = 0, ph_go0 = 0, ph_go1 = 0, ph_staged = 0;
+    Tracer tr(0);
     if (lane != 0) tr.base = nullptr;
     const uint32_t ring_lo = dlo + (ring >> 4);
     for (long long p = blockIdx.x; p < npairs; p += gridDim.x) {
-      const bool have_tile = 2 * p + s < ntiles;                  // last pair of an odd tile count: slot 1 is empty
+      const int nslots = (2 * p + 1 < ntiles) ? 2 : 1;
 #pragma unroll 1
       for (int r = 0; r < NROUND; ++r) {
         const int b0 = plan.round_begin[r], b1 = plan.round_begin[r + 1];
         const uint32_t a_reg = plan.a_reg[r];
-        if (!have_tile) {
-          // nothing to multiply, but the stages still have to be handed back in step with the producer
-          uint32_t st = st0, wph = wph0;
-          for (int b = b0; b < b1; ++b) {
-            mbar_wait(bar_wfull + 8 * st, wph);
-            umma_commit_w(bar_wempty + 8 * st);
-            if (++st == (uint32_t)nst) { st = 0; wph ^= 1; }
-          }
-          st0 = st; wph0 = wph;
-          continue;
-        }
-        {
-          const uint32_t go = bar_go + 32 * s, ph = ph_go;
-          if (r == 0) mbar_wait(bar_staged + 8 * s, ph_staged);   // the stager warp has placed this tile's operands
+#pragma unroll 1
+        for (int s = 0; s < nslots; ++s) {
+          const uint32_t go = bar_go + 32 * s, ph = s ? ph_go1 : ph_go0;
+          if (r == 0) mbar_wait(bar_staged + 8 * s, ph_staged);   // the stager warps have placed this tile's operands
           tr.ev(1, r, s);
           const uint32_t a_ss = dlo + ((sbase + s * MODB) >> 4);
           const uint32_t t_slot = tmem_base + s * 256;
-          // this lane's barrier of the round: lanes 0..3 the go barriers, lanes 8..11 the weight stage of block 0..3
-          uint32_t my_bar = 0, my_par = 0;
-          bool my_act = false;
-          if (lane < 4) { my_bar = go + 8 * lane; my_par = ph; my_act = true; }
-          else if (lane >= 8 && lane < 8 + (b1 - b0)) {
-            const uint32_t stj = st0 + (lane - 8);
-            my_bar = bar_wfull + 8 * (stj >= (uint32_t)nst ? stj - nst : stj);
-            my_par = stj >= (uint32_t)nst ? (wph0 ^ 1) : wph0;
-            my_act = true;
-          }
-          uint32_t ready = 0u;                                    // bits 0..3 go, bits 8..11 weight stages
           uint32_t st = st0, wph = wph0;
-          long long w_go = 0;
+          long long w_go = 0, w_full = 0;                         // traced CTA only: cycles spent waiting
 #pragma unroll 1
           for (int b = b0; b < b1; ++b) {
-            const uint32_t e = blk_s[b];
-            const uint32_t units = e & 0xFF, a0 = (e >> 8) & 0xFF, flags = (e >> 16) & 0xFF, wm = e >> 24;
-            const uint32_t need = wm | (0x100u << (b - b0));
+            const uint32_t units = plan.blk[b].units, a0 = plan.blk[b].a0, flags = plan.blk[b].flags, wm = plan.blk[b].wait;
             const long long tw0 = tr.base ? clock64() : 0;
-            if ((ready & need) != need) {
-              do {
-                bool ok = true;
-                if (my_act) ok = mbar_test(my_bar, my_par);
-                ready |= __ballot_sync(0xffffffffu, ok) & 0xF0Fu;
-              } while ((ready & need) != need);
+            if (wm) {
+              // (every go barrier is waited for in every round: a parity wait cannot tell phases two apart)
+              if (wm & 1) mbar_wait(go, ph);
+              if (wm & 2) mbar_wait(go + 8, ph);
+              if (wm & 4) mbar_wait(go + 16, ph);
+              if (wm & 8) mbar_wait(go + 24, ph);
               tc_fence_after();
             }
-            if (tr.base) { const long long tw1 = clock64(); w_go += tw1 - tw0; tr.ev(7, r, s, (tw1 - tw0) << 16); }
+            const long long tw1 = tr.base ? clock64() : 0;
+            if (s == 0) mbar_wait(bar_wfull + 8 * st, wph);       // slot 1 reuses the stage slot 0 waited for
+            if (tr.base) { const long long tw2 = clock64(); w_go += tw1 - tw0; w_full += tw2 - tw1; }
             const uint32_t b_lo = ring_lo + st * (STAGE >> 4);
             const uint32_t d = t_slot + ((flags & BF_DQ) ? 128 : 0);
             const uint32_t first = (flags & BF_FRESH) ? 0u : 1u;
@@ -385,27 +356,21 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
               }
             }
             tr.ev(5, r, s);
-            umma_commit_w(bar_wempty + 8 * st);                   // this slot's MMAs have read the stage
+            if (s == nslots - 1) umma_commit_w(bar_wempty + 8 * st);   // free once the last slot's MMAs have read it
             if (++st == (uint32_t)nst) { st = 0; wph ^= 1; }
           }
           umma_commit_w(bar_acc + 8 * s);
           if (r == 7) umma_commit_w(bar_r7 + 8 * s);              // fb has read the image features: chunks 0..15 are free
-          // every go barrier is observed in every round (a parity test cannot tell phases two apart): finish the poll
-          while ((ready & 0xFu) != 0xFu) {
-            bool ok = true;
-            if (my_act) ok = mbar_test(my_bar, my_par);
-            ready |= __ballot_sync(0xffffffffu, ok) & 0xF0Fu;
-          }
-          ph_go ^= 1;
-          st0 = st; wph0 = wph;
-          tr.ev(2, r, s, w_go << 20);
+          if (s) ph_go1 ^= 1; else ph_go0 ^= 1;
+          if (s == nslots - 1) { st0 = st; wph0 = wph; }
+          tr.ev(2, r, s, (w_go << 20) | (w_full & 0xFFFFF));
         }
         if (r == 0) ph_staged ^= 1;
       }
     }
     __syncwarp();
-  } else if (warp == 2) {
-    // ================= stager warp ==================================================================
+  } else if (warp == 2 || warp == 3) {
+    // ================= stager warps =================================================================
     // Everything a tile reads from global memory except the image features is brought in HERE, off the epilogue warps'
     // serial chain (a global load issued under this kernel's shared-memory / TMEM traffic takes 2-3 K cycles, a PE
     // rebuild ~4 K): per tile k of slot s and row,
@@ -413,8 +378,7 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
     //   (b) after tile k-1's last FiLM epilogue (modfree):  [film inputs | 1] chunks (K2's operand tile) -> chunks 16.. /
     //       24.. of the slot's 64 KB by cp.async: no registers, all copies of a slot in flight at once
     //   (c) after tile k-1's fb MMAs (r7):                  stash -> chunks 0..7 / 8..15 (the shared-memory operand of L0)
-    //       (cp.async again: the stash has the chunk layout)
-    // then `staged`.  Each lane serves four rows (lane, lane+32, ...) of each slot.
+    // then `staged`.  Each lane serves two rows of each slot (warp 2: rows 0..63, warp 3: 64..127).
     const uint32_t Nu = (uint32_t)N;
     uint32_t ph_mod = 0, ph_r7w = 0;                             // both slots advance in lock step
     for (long long k = 0;; ++k) {
@@ -425,8 +389,8 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
 #pragma unroll 1
       for (int sl = 0; sl < nsl; ++sl) {                          // (a)
 #pragma unroll 1
-        for (int h = 0; h < 4; ++h) {
-          const int row = 32 * h + lane;
+        for (int h = 0; h < 2; ++h) {
+          const int row = (warp - 2) * 64 + 32 * h + lane;
           const uint32_t q = (uint32_t)(t0 + sl) * 128u + row;
           const bool valid = q < Nu;
           float x[3] = {0.f, 0.f, 0.f};
@@ -447,14 +411,13 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
           }
         }
       }
-      __threadfence();                                             // (a)'s stash stores before (c)'s asynchronous reads of them
 #pragma unroll 1
       for (int sl = 0; sl < nsl; ++sl) {
         const uint32_t mod_s = sbase + sl * MODB;
         if (k > 0) mbar_wait_backoff(bar_modfree + 8 * sl, ph_mod);          // (b)
 #pragma unroll 1
-        for (int h = 0; h < 4; ++h) {                              // K2 wrote the operand chunks: copy them verbatim
-          const int row = 32 * h + lane;
+        for (int h = 0; h < 2; ++h) {                              // K2 wrote the operand chunks: copy them verbatim
+          const int row = (warp - 2) * 64 + 32 * h + lane;
           const unsigned char *rec = oper + (t0 + sl) * rec_bytes + row * 16;
 #pragma unroll 1
           for (int c = 0; c < Kf8; ++c) {
@@ -470,13 +433,15 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
         cp_async_commit();
         if (k > 0) mbar_wait_backoff(bar_r7 + 8 * sl, ph_r7w);               // (c)
 #pragma unroll 1
-        for (int h = 0; h < 4; ++h) {
-          const int row = 32 * h + lane;
+        for (int h = 0; h < 2; ++h) {
+          const int row = (warp - 2) * 64 + 32 * h + lane;
           const uint4 *st4 = pe_stash + (((size_t)blockIdx.x * 2 + sl) * 2 + par) * 16 * 128 + row;
-#pragma unroll 1
-          for (int c = 0; c < 16; ++c) cp_async16(mod_s + row * 16 + c * CHUNK, st4 + c * 128);   // this thread's own stores (a)
+          uint4 w[16];
+#pragma unroll
+          for (int c = 0; c < 16; ++c) w[c] = st4[c * 128];                  // this thread's own stores (a)
+#pragma unroll
+          for (int c = 0; c < 16; ++c) sts128(mod_s + row * 16 + c * CHUNK, w[c].x, w[c].y, w[c].z, w[c].w);
         }
-        cp_async_commit();
         cp_async_wait_all();
         __threadfence();                                           // stash and ubuf are read by the epilogue warps
         fence_async_smem();
