@@ -312,6 +312,19 @@ int ucn_select_training_pixels(const float *confidence, int H, int W, int n_rand
                                const long long *coords_rc, int n_depth, uint64_t seed, void *workspace, float *pix_yx,
                                void *stream);
 
+/* The same selection for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  The kernel's workspace
+ * is a file-scope `static __device__` array of ucn_select_static_scratch_bytes() = 33 024 bytes that every GPU loading
+ * the library holds until exit; the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine), the
+ * caller passes inputs and outputs only.  LIMIT: ceil(H*W / 2048) * (patch_num / 2) <= 2048 (the same bound
+ * ucn_select_training_pixels has; e.g. patch_num 16 up to 524 288 pixels); larger requests return UCN_E_ARG.
+ * All calls on one GPU share the array: calls that overlap on the GPU (two streams) race -- serialise them.
+ * Output: bit-identical to ucn_select_training_pixels for the same arguments and seed. */
+size_t ucn_select_static_scratch_bytes(void);
+int ucn_select_training_pixels_static(const float *confidence, int H, int W, int n_rand, int patch_num, int patch_size,
+                                      int crop, const long long *coords_rc, int n_depth, uint64_t seed, float *pix_yx,
+                                      void *stream);
+
 /* ---- multi-GPU: peer-mapped frame buffer (the reference is single-GPU, train.py:433) ------ */
 /* One process per GPU.  The root allocates the [H*W][4]-float frame buffer and exports a 64-byte CUDA IPC handle;
  * every other process opens it with its own device current and passes tile pointers inside it as ucn_render_rays'

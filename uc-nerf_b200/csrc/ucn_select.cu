@@ -14,6 +14,8 @@
 // draws the uniform pixels and appends the coordinates.  Same distribution as the reference, not the same stream.
 #include "ucn_common.cuh"
 
+#include <mutex>
+
 namespace {
 
 constexpr int kT = 256;
@@ -171,5 +173,65 @@ extern "C" int ucn_select_training_pixels(const float *confidence, int H, int W,
   select_pixels_kernel<<<blocks, kT, 0, (cudaStream_t)stream>>>(confidence, H, W, n_rand, half, patch_size, crop, coords_rc, n_depth,
                                                                 seed, cand, counter, pix_yx);
   UCN_LAUNCH_CHECK("select_pixels_kernel");
+  return UCN_OK;
+}
+
+// ---- the same selection for callers that may not allocate (no counterpart in the reference) ---------------------------
+// Added: code under CUDA graph capture, tight serving loops and harnesses that
+// forbid cudaMalloc cannot provide (or let us grow) a workspace.  The workspace of select_pixels_kernel lives in a
+// file-scope device array instead: 256 B (the block counter) + kPerBlock candidates per weight set = 33 024 B, which is
+// the largest workspace ucn_select_training_pixels itself accepts (blocks * half <= kPerBlock), held by every GPU that
+// loads the library until exit.  In host code `g_select_scratch` is only a stand-in for the symbol; the device address is
+// taken once per device with cudaGetSymbolAddress (that device current) and passed to the kernel.
+// Every call shares the array: the counter word is cleared on the caller's stream before each launch (the array keeps the
+// previous call's candidates, which the kernel overwrites before reading), and two calls that OVERLAP on one GPU
+// (different streams, or different host threads' streams) race on it -- serialise them or use the workspace form.
+namespace {
+constexpr size_t kSelectScratchBytes = 256 + (size_t)kPerBlock * 2 * sizeof(Cand);
+static __device__ __align__(256) unsigned char g_select_scratch[kSelectScratchBytes];
+
+cudaError_t select_scratch_address(unsigned char **out) {
+  static unsigned char *addr[kUcnMaxDevices];        // per device: the symbol has one instance per GPU
+  static std::mutex mu;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kUcnMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!addr[dev]) {
+    void *p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_select_scratch);
+    if (e != cudaSuccess) return e;
+    addr[dev] = static_cast<unsigned char *>(p);
+  }
+  *out = addr[dev];
+  return cudaSuccess;
+}
+}  // namespace
+
+extern "C" size_t ucn_select_static_scratch_bytes(void) { return kSelectScratchBytes; }
+
+extern "C" int ucn_select_training_pixels_static(const float *confidence, int H, int W, int n_rand, int patch_num,
+                                                 int patch_size, int crop, const long long *coords_rc, int n_depth,
+                                                 uint64_t seed, float *pix_yx, void *stream) {
+  UCN_CHECK_ARG(confidence && pix_yx, "ucn_select_training_pixels_static: null argument");
+  const int half = patch_num / 2;
+  UCN_CHECK_ARG(H > 0 && W > 0 && patch_size > 0 && n_rand >= 0 && n_depth >= 0 && (n_depth == 0 || coords_rc),
+                "ucn_select_training_pixels_static: bad argument");
+  UCN_CHECK_ARG(half >= 0 && half <= kMaxHalf, "ucn_select_training_pixels_static: at most 128 patches");
+  UCN_CHECK_ARG(H / patch_size >= 2 && W / patch_size >= 2, "ucn_select_training_pixels_static: image smaller than two patches");
+  const long long blocks = ((long long)H * W + kPerBlock - 1) / kPerBlock;
+  if (256 + (size_t)blocks * 2 * (half > 0 ? half : 1) * sizeof(Cand) > kSelectScratchBytes || blocks * half > kPerBlock)
+    return ucn_set_error(UCN_E_ARG, "ucn_select_training_pixels_static: ceil(H*W/2048) * (patch_num/2) exceeds 2048 -- the "
+                                    "33 024-byte static scratch holds no more candidates; use ucn_select_training_pixels");
+  unsigned char *scratch = nullptr;
+  cudaError_t e = select_scratch_address(&scratch);
+  if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_select_training_pixels_static: cudaGetSymbolAddress");
+  e = cudaMemsetAsync(scratch, 0, 256, (cudaStream_t)stream);          // the block counter must start at zero
+  if (e != cudaSuccess) return ucn_cuda_status(e, "ucn_select_training_pixels_static: clear counter");
+  select_pixels_kernel<<<(unsigned)blocks, kT, 0, (cudaStream_t)stream>>>(
+      confidence, H, W, n_rand, half, patch_size, crop, coords_rc, n_depth, seed, reinterpret_cast<Cand *>(scratch + 256),
+      reinterpret_cast<unsigned int *>(scratch), pix_yx);
+  UCN_LAUNCH_CHECK("select_pixels_kernel (static scratch)");
   return UCN_OK;
 }

@@ -101,6 +101,9 @@ _SIGS = {
     "ucn_select_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "ucn_select_training_pixels": (C.c_int, [_fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _fp, C.c_int,
                                              C.c_uint64, _fp, _fp, _fp]),
+    "ucn_select_static_scratch_bytes": (C.c_size_t, []),
+    "ucn_select_training_pixels_static": (C.c_int, [_fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _fp,
+                                                    C.c_int, C.c_uint64, _fp, _fp]),
     "ucn_homo_warp": (C.c_int, [_fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp]),
     "ucn_cost_volume_variance": (C.c_int, [_fp, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp, C.c_int, C.c_int, C.c_int,
                                            _fp, _fp]),
