@@ -8,7 +8,7 @@ lib = L.load()
 V1 = os.environ.get("UCN_X3_KERNEL", "2") == "1"
 set_trace = lib.ucn_debug_set_trace if V1 else lib.ucn_debug_set_trace_p      # round-1 kernel / pipelined kernel
 set_trace.argtypes = [C.c_void_p]
-V, S, R = 3, 126, 148 * 2 * 128 * 6 // 126
+V, S, R = 3, 126, 148 * 2 * 128 * 6 * int(os.environ.get("X3_SCALE", "1")) // 126
 F = 24 + 12 * V + 1
 pw = PackedWeights(synthetic.make_weights(V, seed=0), V, "cuda")
 g = torch.Generator("cuda").manual_seed(0)
@@ -43,6 +43,22 @@ def run():
         L.check(lib.ucn_mlp_forward_tiles(C.byref(pw.c), L.ptr(ndc), L.ptr(feat), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
     else:
         L.check(lib.ucn_mlp_forward_operands(C.byref(pw.c), L.ptr(ndc), L.ptr(rec), L.ptr(ang), R, S, L.ptr(raw), L.MODES["bf16"], L.stream_ptr()), "mlp")
+if os.environ.get("X3_AB"):                       # same-box A/B of debug-flag variants: X3_AB="0,4" -> median ms of each, interleaved
+    sets = [int(x) for x in os.environ["X3_AB"].split(",")]
+    set_flags = lib.ucn_debug_set_flags if V1 else lib.ucn_debug_set_flags_p
+    times = {f: [] for f in sets}
+    for rep in range(7):
+        for f in sets:
+            L.check(set_flags(f), "flags")
+            run(); torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); run(); b.record(); torch.cuda.synchronize()
+            times[f].append(a.elapsed_time(b))
+    L.check(set_flags(0), "flags")
+    for f in sets:
+        t = sorted(times[f])
+        print(f"flags {f}: median {t[len(t) // 2]:.3f} ms  min {t[0]:.3f}  max {t[-1]:.3f}  ({R * S} samples)")
+    sys.exit(0)
 flags = int(os.environ.get("X3_DBG", "0"))
 L.check((lib.ucn_debug_set_flags if V1 else lib.ucn_debug_set_flags_p)(flags), "flags")
 run(); torch.cuda.synchronize()
