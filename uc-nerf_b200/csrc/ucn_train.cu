@@ -333,6 +333,270 @@ split_b_kernel(const float *__restrict__ B, long long sbp, long long sbj, int J,
   }
 }
 
+// ---- the streaming products (forward, grad-input) as a warp-specialised pipeline --------------------------------------
+// gemm_tc_kernel does everything with the same 256 threads: load a slab, convert it, barrier, one thread issues the
+// MMAs, epilogue -- the phases of a tile serialise inside a CTA and only the second resident CTA overlaps them (ncu r01:
+// 1.5 TB/s, 24 % warps active, long-scoreboard 4.2 per issue: too few bytes in flight).  For the two products whose A
+// operand is a [samples x K] activation matrix with 16-byte-aligned rows and whose B operand is a pre-split weight matrix
+// (nn.Linear forward and grad-input: two thirds of the step's products) this kernel gives every phase its own warps,
+// one persistent CTA per SM:
+//   warps 0-1     A loaders: cp.async (16 B per lane and instruction, four full 128-byte lines per warp instruction) of
+//                 raw fp32 slabs [128 rows x 32 p] into a 4-stage ring (64 KB in flight per SM, no registers)
+//   warp 2        B loader: one bulk copy per slab of the pre-split weight slab (24 KB, L2-resident) into a 3-stage ring
+//   warp 3        MMA issuer: six tcgen05.mma per K16 step (the >= 2^-24 terms of the three-part split), accumulators
+//                 double-buffered in TMEM (2 x 128 columns)
+//   warps 4-11    converters: raw fp32 slab -> three bf16 parts in the UMMA core-matrix layout (2-stage operand ring)
+//   warps 12-19   epilogue of tile t while tile t+1 is loaded / converted / multiplied: TMEM -> registers ->
+//                 32 x 32 transposes through shared memory -> bias / accumulate / ReLU -> coalesced 128-byte row stores
+//                 (two warps per TMEM lane quarter, 64 columns each)
+constexpr int WS_THREADS = 640;
+constexpr int WS_RAW_STAGES = 4, WS_AOP_STAGES = 2, WS_B_STAGES = 3;
+constexpr uint32_t WS_RAW = 128 * TC_SLAB * 4;                           // 16 KB raw fp32 slab, row pitch 128 B
+constexpr uint32_t WS_OFF_AOP = WS_RAW_STAGES * WS_RAW;
+constexpr uint32_t WS_OFF_B = WS_OFF_AOP + WS_AOP_STAGES * TC_OPER;
+constexpr uint32_t WS_OFF_TILE = WS_OFF_B + WS_B_STAGES * TC_OPER;
+constexpr uint32_t WS_TILE = 32 * 36 * 4;                                  // per epilogue warp: 32 rows, pitch 36 floats
+constexpr uint32_t WS_OFF_BAR = WS_OFF_TILE + 8 * WS_TILE;
+constexpr uint32_t WS_SMEM = WS_OFF_BAR + 256;
+
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void *src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+template <bool VEC_OUT>
+__global__ void __launch_bounds__(WS_THREADS, 1)
+gemm_ws_kernel(const float *__restrict__ A, long long sai, float *__restrict__ C, long long ldc,
+               const float *__restrict__ bias, int I, int J, int P, int flags, const unsigned char *__restrict__ bsplit) {
+  extern __shared__ __align__(1024) unsigned char ws_smem[];
+  const uint32_t sbase = smem_u32(ws_smem);
+  const uint32_t bars = sbase + WS_OFF_BAR;
+  // barriers (8 bytes each)
+  const uint32_t raw_full = bars, raw_empty = raw_full + 8 * WS_RAW_STAGES, aop_full = raw_empty + 8 * WS_RAW_STAGES,
+                 aop_empty = aop_full + 8 * WS_AOP_STAGES, b_full = aop_empty + 8 * WS_AOP_STAGES,
+                 b_empty = b_full + 8 * WS_B_STAGES, acc_full = b_empty + 8 * WS_B_STAGES, acc_empty = acc_full + 16,
+                 tmem_slot = acc_empty + 16;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int j0 = blockIdx.y * 128, n_tile_i = (I + 127) / 128;
+  const int n_iter = (P + TC_SLAB - 1) / TC_SLAB;
+  if (tid == 0) {
+    for (int i = 0; i < WS_RAW_STAGES; ++i) { mbar_init(raw_full + 8 * i, 64); mbar_init(raw_empty + 8 * i, 8); }
+    for (int i = 0; i < WS_AOP_STAGES; ++i) { mbar_init(aop_full + 8 * i, 8); mbar_init(aop_empty + 8 * i, 1); }
+    for (int i = 0; i < WS_B_STAGES; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(acc_full + 8 * i, 1); mbar_init(acc_empty + 8 * i, 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 3) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(256u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(ws_smem + WS_OFF_BAR + (tmem_slot - bars));
+
+  if (warp < 2) {
+    // ---- A loaders (warp w: rows 64w .. 64w+63 of every slab) ----------------------------------------------------------------------------------------------------
+    uint32_t g = 0;
+    for (int ti = blockIdx.x; ti < n_tile_i; ti += gridDim.x) {
+      const int i0 = ti * 128;
+      for (int it = 0; it < n_iter; ++it, ++g) {
+        const uint32_t rs = g % WS_RAW_STAGES;
+        mbar_wait(raw_empty + 8 * rs, ((g / WS_RAW_STAGES) & 1) ^ 1);
+        const uint32_t dst = sbase + rs * WS_RAW;
+        const int ps = it * TC_SLAB;
+#pragma unroll 8
+        for (int q = 0; q < 16; ++q) {
+          const int f = lane + 32 * q + 512 * warp, r = f >> 3, c4 = f & 7;
+          const int pp = ps + 4 * c4;
+          int nb = (P - pp) * 4;
+          nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+          if (i0 + r >= I) nb = 0;
+          const float *src = nb ? A + (long long)(i0 + r) * sai + pp : A;
+          cp_async16_zfill(dst + r * 128 + ((c4 ^ (r & 7)) << 4), src, (uint32_t)nb);   // XOR swizzle: see the converters
+        }
+        cp_async_mbar_arrive_noinc(raw_full + 8 * rs);
+      }
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+  } else if (warp == 2) {
+    // ---- B loader ----------------------------------------------------------------------------------------------------
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int ti = blockIdx.x; ti < n_tile_i; ti += gridDim.x)
+        for (int it = 0; it < n_iter; ++it, ++g) {
+          const uint32_t bs = g % WS_B_STAGES;
+          mbar_wait(b_empty + 8 * bs, ((g / WS_B_STAGES) & 1) ^ 1);
+          mbar_expect_tx(b_full + 8 * bs, TC_OPER);
+          bulk_g2s(sbase + WS_OFF_B + bs * TC_OPER, bsplit + ((size_t)blockIdx.y * n_iter + it) * TC_OPER, TC_OPER,
+                   b_full + 8 * bs);
+        }
+    }
+    __syncwarp();
+  } else if (warp == 3) {
+    // ---- MMA issuer --------------------------------------------------------------------------------------------------
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(128);
+      uint32_t g = 0, t = 0;
+      for (int ti = blockIdx.x; ti < n_tile_i; ti += gridDim.x, ++t) {
+        const uint32_t buf = t & 1;
+        mbar_wait(acc_empty + 8 * buf, ((t >> 1) & 1) ^ 1);            // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d = tmem_base + 128 * buf;
+        for (int it = 0; it < n_iter; ++it, ++g) {
+          const uint32_t as = g % WS_AOP_STAGES, bs = g % WS_B_STAGES;
+          mbar_wait(aop_full + 8 * as, (g / WS_AOP_STAGES) & 1);
+          mbar_wait(b_full + 8 * bs, (g / WS_B_STAGES) & 1);
+          tc_fence_after();
+          const uint32_t a0 = sbase + WS_OFF_AOP + as * TC_OPER, b0 = sbase + WS_OFF_B + bs * TC_OPER;
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            uint64_t da[TC_PARTS], db[TC_PARTS];
+#pragma unroll
+            for (int pt = 0; pt < TC_PARTS; ++pt) {
+              da[pt] = umma_desc(a0 + pt * TC_PART + u * 2 * TC_CHUNK, TC_CHUNK, 128);
+              db[pt] = umma_desc(b0 + pt * TC_PART + u * 2 * TC_CHUNK, TC_CHUNK, 128);
+            }
+            umma_ss(d, da[0], db[0], idesc, (it > 0 || u > 0) ? 1u : 0u);
+            umma_ss(d, da[0], db[1], idesc, 1u);
+            umma_ss(d, da[1], db[0], idesc, 1u);
+            umma_ss(d, da[0], db[2], idesc, 1u);
+            umma_ss(d, da[1], db[1], idesc, 1u);
+            umma_ss(d, da[2], db[0], idesc, 1u);
+          }
+          umma_commit(aop_empty + 8 * as);
+          umma_commit(b_empty + 8 * bs);
+        }
+        umma_commit(acc_full + 8 * buf);
+      }
+    }
+    __syncwarp();
+  } else if (warp < 12) {
+    // ---- converters: raw fp32 slab -> three bf16 parts in the UMMA K-major core-matrix layout -----------------------------
+    const int ct = tid - 128;
+    uint32_t g = 0;
+    for (int ti = blockIdx.x; ti < n_tile_i; ti += gridDim.x)
+      for (int it = 0; it < n_iter; ++it, ++g) {
+        const uint32_t rs = g % WS_RAW_STAGES, as = g % WS_AOP_STAGES;
+        mbar_wait(raw_full + 8 * rs, (g / WS_RAW_STAGES) & 1);
+        mbar_wait(aop_empty + 8 * as, ((g / WS_AOP_STAGES) & 1) ^ 1);     // the MMAs of slab g-2 have read this stage
+        const uint32_t raw = sbase + rs * WS_RAW, base = sbase + WS_OFF_AOP + as * TC_OPER;
+        // lane -> (row, 16-byte column): 8 consecutive lanes take 8 consecutive rows of ONE column, the next 8 the column's
+        // pair, lanes 16-31 the next 8 rows.  With the loader's XOR swizzle a quarter-warp's 128-bit loads hit eight
+        // different 16-byte bank groups, and a half-warp's 64-bit stores fill one 128-byte row of banks of the operand
+        // chunk (8 rows x 16 B): both directions conflict-free (the row-major mapping stored with 4-way conflicts, which
+        // made the shared-memory pipe -- shared with the MMAs' operand reads -- the limiter).
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int r = (ct & 7) | (((ct >> 4) & 1) << 3) | ((ct >> 5) << 4), c4 = ((ct >> 3) & 1) | (q << 1);
+          const uint4 v = lds128(raw + r * 128 + ((c4 ^ (r & 7)) << 4));
+          uint32_t w0[3], w1[3];
+          split3(__uint_as_float(v.x), __uint_as_float(v.y), w0);
+          split3(__uint_as_float(v.z), __uint_as_float(v.w), w1);
+          const uint32_t addr = base + (c4 >> 1) * TC_CHUNK + r * 16 + (c4 & 1) * 8;
+#pragma unroll
+          for (int pt = 0; pt < TC_PARTS; ++pt)
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr + pt * TC_PART), "r"(w0[pt]), "r"(w1[pt]) : "memory");
+        }
+        fence_async_smem();                                            // generic-proxy stores -> the MMA's async-proxy reads
+        __syncwarp();
+        if (lane == 0) { mbar_arrive(aop_full + 8 * as); mbar_arrive(raw_empty + 8 * rs); }
+      }
+  } else {
+    // ---- epilogue warps: warp w owns TMEM lanes 32*(w%4).. (rows), all 128 columns of the tile ----------------------------
+    const int q = warp & 3;
+    const int ch = (warp - 12) >> 2;                                 // this warp's column half: chunks 64*ch, 64*ch + 32
+    float *tile = reinterpret_cast<float *>(ws_smem + WS_OFF_TILE + (warp - 12) * WS_TILE);
+    const uint32_t tile_a = sbase + WS_OFF_TILE + (warp - 12) * WS_TILE;
+    const bool accum = flags & G_ACCUM, relu = flags & G_RELU;
+    float4 bias4[2];                                                 // this lane's four columns of its two chunks (VEC_OUT)
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      const int j = j0 + 64 * ch + 32 * cc + 4 * (lane & 7);
+      bias4[cc] = (VEC_OUT && bias && j < J) ? *reinterpret_cast<const float4 *>(bias + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    uint32_t t = 0;
+    for (int ti = blockIdx.x; ti < n_tile_i; ti += gridDim.x, ++t) {
+      const int i0 = ti * 128;
+      const uint32_t buf = t & 1;
+      mbar_wait_backoff(acc_full + 8 * buf, (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + 128 * buf;
+      const int nrow = min(32, I - (i0 + 32 * q));                    // rows of this warp's quarter inside the matrix
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c0 = 64 * ch + 32 * cc;
+        uint32_t acc[32];
+        tmem_ld32(taddr + c0, acc);
+        tmem_wait_ld();
+        if (VEC_OUT) {
+          // 32 x 32 transpose through shared memory in 16-byte pieces (row pitch 144 B: conflict-free both ways), so that a
+          // warp instruction writes four full 128-byte lines: 8 STS.128 + 8 LDS.128 + 8 STG.128 per thread and chunk (the
+          // scalar form below costs 2.4 K instructions per tile and warp and was the kernel's bottleneck)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) sts128(tile_a + lane * 144 + k * 16, acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
+          __syncwarp();
+          const int cq = lane & 7, rq = lane >> 3;
+          const int j = j0 + c0 + 4 * cq;                             // J % 4 == 0: the four columns are inside or outside together
+          if (j < J) {
+            const float4 b4 = bias4[cc];
+            float *dst = C + (long long)(i0 + 32 * q + rq) * ldc + j;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+              const uint4 w = lds128(tile_a + (4 * b + rq) * 144 + cq * 16);
+              float4 v = make_float4(__uint_as_float(w.x) + b4.x, __uint_as_float(w.y) + b4.y, __uint_as_float(w.z) + b4.z,
+                                     __uint_as_float(w.w) + b4.w);
+              if (4 * b + rq < nrow) {
+                float4 *d4 = reinterpret_cast<float4 *>(dst + (long long)(4 * b) * ldc);
+                if (accum) { const float4 o = *d4; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+                if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+                *d4 = v;
+              }
+            }
+          }
+          __syncwarp();
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) tile[lane * 36 + c] = __uint_as_float(acc[c]);
+          __syncwarp();
+          const int j = j0 + c0 + lane;
+          const float bj = (bias && j < J) ? bias[j] : 0.0f;
+          if (j < J) {
+            float *dst = C + (long long)(i0 + 32 * q) * ldc + j;
+#pragma unroll 1
+            for (int r0 = 0; r0 < 32; r0 += 8) {
+              float v[8];
+#pragma unroll
+              for (int k = 0; k < 8; ++k) v[k] = tile[(r0 + k) * 36 + lane] + bj;
+              if (accum) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) if (r0 + k < nrow) v[k] += dst[(long long)(r0 + k) * ldc];
+              }
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                if (relu) v[k] = fmaxf(v[k], 0.0f);
+                if (r0 + k < nrow) dst[(long long)(r0 + k) * ldc] = v[k];
+              }
+            }
+          }
+          __syncwarp();
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty + 8 * buf);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 3) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
+  }
+}
+
 // ---- the 3- and 1-wide heads (confi_rgb / alpha_1 / rgb / alpha, network/models.py:161-162,170,174) ------------------
 // A 64- or 128-wide GEMM tile would be >95 % padding there; these three kernels stream the wide operand once, coalesced.
 // forward: warp per row, lanes over k, shuffle reduction.  Y[m][n] (+)= sum_k X[m][k] W[n][k] + b[n], N <= 4
@@ -735,6 +999,25 @@ int launch_gemm(const float *A, long long sai, long long sap, const float *B, lo
     if (bsplit) {
       split_b_kernel<<<dim3((unsigned)n_iter, grid.y), 256, 0, (cudaStream_t)stream>>>(B, sbp, sbj, (int)J, P, n_iter, bsplit);
       UCN_LAUNCH_CHECK("split_b_kernel");
+    }
+    // forward / grad-input with aligned activation rows: the warp-specialised pipeline (one persistent CTA per SM)
+    if (bsplit && a_vec && !(flags & G_ATOMIC) && !(g_gemm_dbg & 64) && P < (1ll << 30)) {
+      static int attr_ws[kUcnMaxDevices];
+      static int attr_ws2[kUcnMaxDevices];
+      // 16-byte output stores need aligned rows of C (grad-input of the [PE63 | h] layer writes rows of 191 floats: scalar form)
+      const bool vec_out = (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (J & 3) == 0 &&
+                           (!bias || (reinterpret_cast<uintptr_t>(bias) & 15) == 0);
+      cudaError_t e = vec_out ? ucn_ensure_dyn_smem(gemm_ws_kernel<true>, (int)WS_SMEM, attr_ws)
+                              : ucn_ensure_dyn_smem(gemm_ws_kernel<false>, (int)WS_SMEM, attr_ws2);
+      if (e != cudaSuccess) return ucn_cuda_status(e, "gemm_ws smem attribute");
+      const unsigned cap = (unsigned)ucn_sm_count() / grid.y;
+      dim3 g2(cap >= 1 && grid.x > cap ? cap : grid.x, grid.y, 1);
+      if (vec_out)
+        gemm_ws_kernel<true><<<g2, WS_THREADS, WS_SMEM, (cudaStream_t)stream>>>(A, sai, C, ldc, bias, (int)I, (int)J, (int)P, flags, bsplit);
+      else
+        gemm_ws_kernel<false><<<g2, WS_THREADS, WS_SMEM, (cudaStream_t)stream>>>(A, sai, C, ldc, bias, (int)I, (int)J, (int)P, flags, bsplit);
+      UCN_LAUNCH_CHECK("gemm_ws_kernel");
+      return UCN_OK;
     }
     if (!(g_gemm_dbg & 32)) {
       const int sms = ucn_sm_count();
