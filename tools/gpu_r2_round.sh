@@ -1,5 +1,5 @@
 #!/bin/bash
-# one GPU-box visit (round 2): parity tests, smoke, bench (+ reference arm), ncu launch list, ncu --set full of the hot-path kernels at C2
+# one GPU-box visit (round 2): parity tests, smoke, bench (+ reference arm), ncu launch list (the --set full capture is tools/gpu_r2_g.sh: one ncu per visit)
 tag=${1:-a}
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
@@ -9,5 +9,4 @@ timeout -s KILL 400 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_r2$
 timeout -s KILL 200 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_r2$tag.json 2> gpurun_out/bench_ref_r2$tag.err; echo "ref rc=$?"; cut -c1-400 gpurun_out/bench_ref_r2$tag.json
 timeout -s KILL 300 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras > gpurun_out/plain_r2$tag.log 2>&1 && \
 timeout -s KILL 500 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_r2$tag.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras > gpurun_out/ncu_launch_r2$tag.log 2>&1; echo "ncu launches rc=$?"
-timeout -s KILL 600 ncu --set full --clock-control none --import-source on -k regex:'mlp_x3p_kernel|gather_kernel|composite_kernel|raygen_sample_kernel|ray_term_kernel' -s 30 -c 5 -o gpurun_out/full_r2$tag -f python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-extras > gpurun_out/ncu_full_r2$tag.log 2>&1; echo "ncu full rc=$?"
 ls -la gpurun_out | tail -8
