@@ -217,7 +217,7 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
     rgb = torch.empty((n_tile, 3), device=dev)
     depth = torch.empty((n_tile,), device=dev)
     flag = torch.zeros(1, device=dev)
-    ren_box, bar_ev = {}, []
+    ren_box, bar_ev, host_submit = {}, [], {}
 
     def step_resident(timers, seed, i=0):
         fr = pack(resident)
@@ -261,11 +261,13 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
         for i in range(n):
             fn(i)
         e1.record()
+        submit = (time.perf_counter() - t0) * 1e3        # host time to SUBMIT the n steps (no synchronisation inside)
         barrier()
         wall = (time.perf_counter() - t0) * 1e3
-        ms = torch.tensor([e0.elapsed_time(e1), wall], device=dev, dtype=torch.float64)
+        ms = torch.tensor([e0.elapsed_time(e1), wall, submit], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        host_submit["ms"] = ms[2].item() / n
         return ms[0].item() / n, ms[1].item() / n
 
     for i in range(warmup):
@@ -283,6 +285,7 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
     bar_ev.clear()
     L.launch_count(reset=True)
     ms, wall_ms = timed(lambda i: step_resident(None, i, i), steps)
+    submit_ms = host_submit.get("ms")
     launches = L.launch_count() // steps
     gather_ev = list(bar_ev)
     timers = {}
@@ -324,6 +327,23 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
         barrier()
 
     kern = {k: sum(a.elapsed_time(b) for a, b in v) / steps for k, v in timers.items()}   # ms per step, this rank
+    # GPU timeline of the instrumented pass on this rank: what lies BETWEEN the kernels of a frame and between frames
+    # (event to event, so idle time shows up): diagnostic for the multi-GPU frame period
+    timeline = None
+    order = [k for k in ("raygen", "dir", "gather", "mlp", "composite") if k in timers]
+    if order and all(len(timers[k]) == steps for k in order) and steps > 1:
+        gaps = {}
+        for a, b in zip(order, order[1:]):
+            gaps[f"{a}->{b}"] = sum(timers[a][i][1].elapsed_time(timers[b][i][0]) for i in range(steps)) / steps
+        gaps["frame_end->next_frame_first_kernel"] = sum(timers[order[-1]][i][1].elapsed_time(timers[order[0]][i + 1][0])
+                                                         for i in range(steps - 1)) / (steps - 1)
+        timeline = {"instrumented_ms_per_step": ms_instr, "gaps_ms": {k: round(v, 4) for k, v in gaps.items()}}
+    per_rank = None
+    if world > 1:
+        mine = torch.tensor([sum(kern.values())], device=dev, dtype=torch.float64)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = [round(float(t.item()), 4) for t in allr]
     n_launch = {k: len(v) // steps for k, v in timers.items()}
     h2d_rank = sweep.h2d_bytes(host)
     tot = torch.tensor([float(h2d_rank)], device=dev, dtype=torch.float64)
@@ -354,7 +374,7 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
         else:
             par = "single GPU, whole frame"
         res = {
-            "value": total_rays / (ms * 1e-3), "ms_per_step": ms, "wall_ms_per_step": wall_ms,
+            "value": total_rays / (ms * 1e-3), "ms_per_step": ms, "wall_ms_per_step": wall_ms, "host_submit_ms_per_step": submit_ms,
             "scaling": "strong" if split else "weak",
             "config": {"workload": wl["name"], "H": H, "W": W, "source_views": V, "samples_per_ray": S,
                        "mlp_mode": args.mode, "rays_per_launch_group": max_rays, "rays_per_rank": n_tile,
@@ -386,6 +406,8 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
                              "(4-byte all-reduce) on rank 0, which includes waiting for the slowest rank") if peer_mode \
                 else "ncclAllGather of the [R/P,4] tiles (shard.gather_image)"
             res["checks"] = checks
+            res["per_rank_kernel_ms"] = per_rank            # sum of the rank's kernels per frame (instrumented pass)
+            res["timeline"] = timeline
         # ---- parity of the timed configuration: a band of the same frame on the GPU vs the CPU oracle, same jitter ----
         from oracle import oracle as O
         osc, ow = O.OracleScene(sc, S, dir_switch=1024), O.OracleWeights(wts, V)
@@ -516,7 +538,8 @@ def main():
                 "scaling": res["scaling"], "vs_baseline": None, "dtype": "f32" if args.mode == "fp32" else "bf16",
                 "data": "synthetic"}
         for k in ("config", "e2e", "gpu_launches", "clocks", "roofline", "kernels_ms_per_step", "kernels_from", "hbm_kernels",
-                  "wall_ms_per_step", "gather_ms", "gather", "checks", "parity", "cpu_baseline"):
+                  "wall_ms_per_step", "host_submit_ms_per_step", "gather_ms", "gather", "per_rank_kernel_ms", "timeline", "checks", "parity",
+                  "cpu_baseline"):
             if k in res and res[k] is not None:
                 line[k] = res[k]
         if "gpu_eager_baseline" in extra:
