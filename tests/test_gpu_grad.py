@@ -84,6 +84,42 @@ def test_linear_primitives_match_torch(gemm_mode, tol):
         L.check(L.load().ucn_train_gemm_mode(0))
 
 
+def test_warp_specialised_gemm_matches_the_single_role_kernel():
+    """gemm_ws_kernel (forward / grad-input with 16-byte-aligned activation rows) against gemm_tc_kernel (debug flag 64
+    routes the same call to it) and torch fp64: ragged row counts, partial 32-wide slabs, partial column tiles, the
+    vector (ldc % 4 == 0) and scalar output forms, bias / accumulate / ReLU.  Both kernels issue the same six MMAs per
+    K16 step on the same three-part operands, so the outputs must be bit-identical."""
+    from ucnerf_b200 import lib as L
+    lib = L.load()
+    lib.ucn_debug_gemm_flags.argtypes = [C.c_int]
+    g = torch.Generator(device="cpu").manual_seed(3)
+    try:
+        for M, K, N, ldy in ((1000, 40, 128, 128), (1153, 128, 64, 64), (2500, 192, 200, 200), (1100, 128, 130, 131),
+                             (4096, 100, 128, 132), (20000, 128, 256, 256)):
+            X = torch.randn((M, K), generator=g).to(DEV)
+            W = torch.randn((N, K), generator=g).to(DEV)
+            b = torch.randn((N + 3,), generator=g).to(DEV)[:N].contiguous()
+            seed = torch.randn((M, ldy), generator=g).to(DEV)
+            ref = X.double() @ W.double().t() + b.double()
+            for flags in (0, 1, 3):                      # plain, accumulate, accumulate + ReLU
+                outs = []
+                for dbg in (64, 0):
+                    lib.ucn_debug_gemm_flags(dbg)
+                    Y = seed.clone()
+                    L.check(lib.ucn_linear_fwd(L.ptr(X), K, L.ptr(W), K, L.ptr(b), M, K, N, L.ptr(Y), ldy, flags, L.stream_ptr()),
+                            "ucn_linear_fwd")
+                    outs.append(Y)
+                assert torch.equal(outs[0], outs[1]), (M, K, N, ldy, flags)
+                want = ref + (seed[:, :N].double() if flags & 1 else 0.0)
+                if flags & 2:
+                    want = torch.relu(want)
+                assert rel_err(outs[1][:, :N].cpu().numpy(), want.cpu().numpy()) <= 1e-5, (M, K, N, flags)
+                if ldy > N:
+                    assert torch.equal(outs[1][:, N:], seed[:, N:]), "columns beyond N must stay untouched"
+    finally:
+        lib.ucn_debug_gemm_flags(0)
+
+
 @pytest.mark.parametrize("name", GRAD_CASES)
 def test_composite_backward(name):
     from ucnerf_b200 import lib as L
