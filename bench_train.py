@@ -240,7 +240,7 @@ def measure(args, ClockSampler, peaks, ctx, full=True):
             "e2e": {"value": world * R / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": n_depth * 16,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
             "gpu_launches": launches, "clocks": clocks,
-            "roofline": {"kernel": "gemm_ws_kernel + gemm_tc_kernel (nn.Linear forward / grad-input / grad-weight on tcgen05, three bf16 parts per fp32 operand)", "bound": "tensor",
+            "roofline": {"kernel": "gemm_ws_kernel + gemm_wsw_kernel + gemm_tc_kernel (nn.Linear forward / grad-input / grad-weight on tcgen05, three bf16 parts per fp32 operand)", "bound": "tensor",
                          "achieved": achieved, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
                          "frac": achieved / pk["bf16_tflops_sustained"], "traffic": None,
                          "peak_source": pk["_source"] + " (bf16_tflops_sustained)",

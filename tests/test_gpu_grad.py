@@ -120,6 +120,38 @@ def test_warp_specialised_gemm_matches_the_single_role_kernel():
         lib.ucn_debug_gemm_flags(0)
 
 
+def test_mn_major_grad_weight_pipeline_matches_fp64():
+    """gemm_wsw_kernel (grad-weight over >= 4096 samples, both operands staged in their natural layout as MN-major UMMA
+    operands) against torch fp64 and against gemm_tc_kernel's split reduction (debug flag 128): ragged sample counts (a
+    partial last 32-sample slab), partial output tiles in both directions, two column tiles, X views with a wider pitch,
+    accumulation into a non-zero dW, and the forced 4-byte staging of an unaligned X (flag 256)."""
+    from ucnerf_b200 import lib as L
+    lib = L.load()
+    lib.ucn_debug_gemm_flags.argtypes = [C.c_int]
+    g = torch.Generator(device="cpu").manual_seed(5)
+    try:
+        for M, K, N, ldx, dbg in ((5000, 128, 128, 128, 0), (4100, 191, 128, 192, 0), (9001, 63, 256, 192, 0),
+                                  (4097, 40, 64, 40, 0), (20000, 155, 128, 160, 0), (4500, 37, 128, 37, 256)):
+            Xb = torch.randn((M, ldx), generator=g).to(DEV)
+            X = Xb[:, :K]
+            dY = torch.randn((M, N), generator=g).to(DEV)
+            init = torch.randn((N, K + 2), generator=g).to(DEV)
+            ref = init[:, :K].double() + dY.double().t() @ X.double()
+            outs = []
+            for fl in (128, dbg):
+                lib.ucn_debug_gemm_flags(fl)
+                dW, db = init.clone(), torch.zeros((N,), device=DEV)
+                L.check(lib.ucn_linear_bwd_weight(L.ptr(dY), N, L.ptr(Xb), ldx, M, K, N, L.ptr(dW), K + 2, L.ptr(db), L.stream_ptr()),
+                        "ucn_linear_bwd_weight")
+                outs.append(dW)
+                assert rel_err(dW[:, :K].cpu().numpy(), ref.cpu().numpy()) <= 1e-5, (M, K, N, fl)
+                assert torch.equal(dW[:, K:], init[:, K:]), "columns beyond K must stay untouched"
+                assert rel_err(db.cpu().numpy(), dY.double().sum(0).cpu().numpy()) <= 1e-5
+            assert rel_err(outs[1][:, :K].cpu().numpy(), outs[0][:, :K].cpu().numpy()) <= 1e-5
+    finally:
+        lib.ucn_debug_gemm_flags(0)
+
+
 @pytest.mark.parametrize("name", GRAD_CASES)
 def test_composite_backward(name):
     from ucnerf_b200 import lib as L

@@ -23,13 +23,13 @@ for K in (128, 64, 191):
         print(f"K={K} flags={fl:2d}: {e0.elapsed_time(e1) / 20 * 1e3:8.1f} us", flush=True)
 lib.ucn_debug_gemm_flags(0)
 
-# grad-weight product dW[128][K] += dY^T X, reduction over M split across CTAs (flags >> 8 overrides the split count)
+# grad-weight product dW[128][K] += dY^T X, reduction over M split across CTAs (flags >> 12 overrides the split count)
 lib.ucn_linear_bwd_weight.restype = C.c_int
 for K in (128, 64):
     X = torch.randn(M, K, device="cuda"); dY = torch.randn(M, 128, device="cuda")
     dW = torch.zeros(128, K, device="cuda")
     for sp in (0, 74, 148, 222, 296, 444, 592, 888):
-        lib.ucn_debug_gemm_flags(sp << 8)
+        lib.ucn_debug_gemm_flags((sp << 12) | 128)
         def run():
             L.check(lib.ucn_linear_bwd_weight(L.ptr(dY), 128, L.ptr(X), X.stride(0), M, K, 128, L.ptr(dW), K, None, L.stream_ptr()), "bwdw")
         for _ in range(3): run()

@@ -30,3 +30,30 @@ for K, N in [(int(a), int(b)) for a, b in (x.split("x") for x in os.environ.get(
     print(f"   max|ws-old| {float((outs[0] - outs[64]).abs().max()):.3e}   max|ws-fp64| {float((outs[0][:4096] - ref).abs().max()):.3e}"
           f"   max|old-fp64| {float((outs[64][:4096] - ref).abs().max()):.3e}", flush=True)
 lib.ucn_debug_gemm_flags(0)
+
+# grad-weight dW[N][K] += dY^T X: gemm_tc_kernel with split reduction (flag 128) against the MN-major pipeline gemm_wsw_kernel
+if os.environ.get("GEMM_BWDW", "1") == "1":
+    for K, N, ldx in ((128, 128, 128), (64, 128, 64), (191, 128, 191), (128, 256, 128), (37, 128, 37), (155, 128, 155)):
+        Xb = torch.randn(M, ldx, device="cuda"); X = Xb[:, :K]
+        dY = torch.randn(M, N, device="cuda")
+        outs = {}
+        for fl in (128, 0, 128, 0):
+            lib.ucn_debug_gemm_flags(fl)
+            dW = torch.zeros(N, K, device="cuda")
+            def run():
+                L.check(lib.ucn_linear_bwd_weight(L.ptr(dY), N, L.ptr(Xb), ldx, M, K, N, L.ptr(dW), K, None, L.stream_ptr()), "bwdw")
+            run(); torch.cuda.synchronize()
+            outs[fl] = dW.clone()
+            for _ in range(2): run()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20): run()
+            e1.record(); torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) / 20 * 1e3
+            gb = (M * K + M * N) * 4 / 1e9
+            print(f"bwd_weight K={K} N={N} ldx={ldx} {'old' if fl else 'wsw'}: {us:8.1f} us  {gb / us * 1e6 / 1e3:6.2f} TB/s", flush=True)
+        ref = (dY.double().t() @ X.double()).float()
+        sc = float(ref.abs().max())
+        print(f"   rel max|wsw-fp64| {float((outs[0] - ref).abs().max()) / sc:.3e}   rel max|old-fp64| {float((outs[128] - ref).abs().max()) / sc:.3e}", flush=True)
+    lib.ucn_debug_gemm_flags(0)

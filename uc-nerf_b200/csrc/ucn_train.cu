@@ -597,6 +597,196 @@ gemm_ws_kernel(const float *__restrict__ A, long long sai, float *__restrict__ C
   }
 }
 
+// ---- the grad-weight product as the same kind of pipeline ----------------------------------------------------------------
+// dW[i][j] += sum_p dY[p][i] X[p][j]: both operands are activation matrices whose CONTIGUOUS index is the output index, not
+// the reduction index.  gemm_tc_kernel stages them thread = row with scalar loads and converts both in every CTA: its time
+// does not depend on K (105 us at K = 64 and K = 128, M = 258 048) -- conversion- and latency-bound, not HBM-bound.  Here the
+// raw [32 samples x 128] fp32 slabs go straight into shared memory by cp.async and are converted in their natural order into
+// MN-MAJOR operands (UMMA no-swizzle MN-major: 8 consecutive output indices are the 16 contiguous bytes of a core-matrix row,
+// the 8 reduction steps of a core matrix are 16 bytes apart; element (mn, k) at (k/8)*LBO + (mn/8)*SBO + (k%8)*16 + (mn%8)*2
+// with SBO = 128, LBO = 2048): no transposition anywhere.  One persistent CTA per SM and output tile takes a contiguous range
+// of the reduction, accumulates the 128 x 128 tile in TMEM and adds it to dW with coalesced fp32 atomics at the end.
+//   warp 0        dY loader (cp.async 16 B)          warps 1-2   X loader (16 B, or 4 B when X's rows are not 16-byte aligned)
+//   warp 3        MMA issuer                          warps 4-19  converters (8: dY, 8: X), then the epilogue
+constexpr int WW_STAGES = 3;
+constexpr uint32_t WW_RAW = 32 * 128 * 4;                                 // one operand's raw slab: 32 samples x 128 floats
+constexpr uint32_t WW_OFF_OP = WW_STAGES * 2 * WW_RAW;
+constexpr uint32_t WW_OFF_BAR = WW_OFF_OP + 2 * 2 * TC_OPER;
+constexpr uint32_t WW_SMEM = WW_OFF_BAR + 256;
+
+__device__ __forceinline__ void cp_async4_zfill(uint32_t dst, const void *src, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ uint32_t umma_idesc_bf16_mn(int N) {          // as umma_idesc_bf16, A and B MN-major
+  return umma_idesc_bf16(N) | (1u << 15) | (1u << 16);
+}
+
+template <bool X_VEC>
+__global__ void __launch_bounds__(WS_THREADS, 1)
+gemm_wsw_kernel(const float *__restrict__ dY, long long ldy, const float *__restrict__ X, long long ldx,
+                float *__restrict__ C, long long ldc, int I, int J, long long P, int slabs_per_cta) {
+  extern __shared__ __align__(1024) unsigned char ww_smem[];
+  const uint32_t sbase = smem_u32(ww_smem);
+  const uint32_t bars = sbase + WW_OFF_BAR;
+  const uint32_t rawa_full = bars, rawb_full = rawa_full + 8 * WW_STAGES, raw_empty = rawb_full + 8 * WW_STAGES,
+                 op_full = raw_empty + 8 * WW_STAGES, op_empty = op_full + 16, acc_full = op_empty + 16, tmem_slot = acc_full + 8;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n_tj = (J + 127) / 128;
+  const int i0 = ((int)blockIdx.y / n_tj) * 128, j0 = ((int)blockIdx.y % n_tj) * 128;
+  const long long n_slab_all = (P + TC_SLAB - 1) / TC_SLAB;
+  const long long s_begin = (long long)blockIdx.x * slabs_per_cta;
+  const int n_slab = (int)max(0ll, min((long long)slabs_per_cta, n_slab_all - s_begin));
+  if (tid == 0) {
+    for (int i = 0; i < WW_STAGES; ++i) {
+      mbar_init(rawa_full + 8 * i, 32); mbar_init(rawb_full + 8 * i, 64); mbar_init(raw_empty + 8 * i, 16);
+    }
+    for (int i = 0; i < 2; ++i) { mbar_init(op_full + 8 * i, 16); mbar_init(op_empty + 8 * i, 1); }
+    mbar_init(acc_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 3) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(ww_smem + WW_OFF_BAR + (tmem_slot - bars));
+
+  if (warp == 0) {
+    // ---- dY loader: 32 samples x 128 output rows i0.. of dY, 16 bytes per lane and instruction ------------------------------
+    for (int g = 0; g < n_slab; ++g) {
+      const uint32_t rs = g % WW_STAGES;
+      mbar_wait(raw_empty + 8 * rs, ((g / WW_STAGES) & 1) ^ 1);
+      const uint32_t dst = sbase + rs * 2 * WW_RAW;
+      const long long p0 = (s_begin + g) * TC_SLAB;
+#pragma unroll 8
+      for (int q = 0; q < 32; ++q) {
+        const int f = lane + 32 * q, pl = f >> 5, c4 = f & 31;
+        int nb = (I - i0 - 4 * c4) * 4;
+        nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+        if (p0 + pl >= P) nb = 0;
+        const float *src = nb ? dY + (p0 + pl) * ldy + i0 + 4 * c4 : dY;
+        cp_async16_zfill(dst + pl * 512 + ((c4 ^ (pl & 7)) << 4), src, (uint32_t)nb);
+      }
+      cp_async_mbar_arrive_noinc(rawa_full + 8 * rs);
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+  } else if (warp < 3) {
+    // ---- X loaders (warp 1: samples 0..15 of a slab, warp 2: 16..31) -----------------------------------------------------------
+    const int wh = warp - 1;
+    for (int g = 0; g < n_slab; ++g) {
+      const uint32_t rs = g % WW_STAGES;
+      mbar_wait(raw_empty + 8 * rs, ((g / WW_STAGES) & 1) ^ 1);
+      const uint32_t dst = sbase + rs * 2 * WW_RAW + WW_RAW;
+      const long long p0 = (s_begin + g) * TC_SLAB;
+      if (X_VEC) {
+#pragma unroll 8
+        for (int q = 0; q < 16; ++q) {
+          const int f = lane + 32 * q + 512 * wh, pl = f >> 5, c4 = f & 31;
+          int nb = (J - j0 - 4 * c4) * 4;
+          nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+          if (p0 + pl >= P) nb = 0;
+          const float *src = nb ? X + (p0 + pl) * ldx + j0 + 4 * c4 : X;
+          cp_async16_zfill(dst + pl * 512 + ((c4 ^ (pl & 7)) << 4), src, (uint32_t)nb);
+        }
+      } else {
+#pragma unroll 8
+        for (int q = 0; q < 64; ++q) {
+          const int e = lane + 32 * q + 2048 * wh, pl = e >> 7, j = e & 127;
+          const bool ok = p0 + pl < P && j0 + j < J;
+          const float *src = ok ? X + (p0 + pl) * ldx + j0 + j : X;
+          cp_async4_zfill(dst + pl * 512 + ((((j >> 2) ^ (pl & 7))) << 4) + (j & 3) * 4, src, ok ? 4u : 0u);
+        }
+      }
+      cp_async_mbar_arrive_noinc(rawb_full + 8 * rs);
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+  } else if (warp == 3) {
+    // ---- MMA issuer ---------------------------------------------------------------------------------------------------------------
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16_mn(128);
+      for (int g = 0; g < n_slab; ++g) {
+        const uint32_t os = g & 1;
+        mbar_wait(op_full + 8 * os, (g >> 1) & 1);
+        tc_fence_after();
+        const uint32_t a0 = sbase + WW_OFF_OP + os * 2 * TC_OPER, b0 = a0 + TC_OPER;
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          uint64_t da[TC_PARTS], db[TC_PARTS];
+#pragma unroll
+          for (int pt = 0; pt < TC_PARTS; ++pt) {
+            da[pt] = umma_desc(a0 + pt * TC_PART + u * 2 * TC_CHUNK, TC_CHUNK, 128);
+            db[pt] = umma_desc(b0 + pt * TC_PART + u * 2 * TC_CHUNK, TC_CHUNK, 128);
+          }
+          umma_ss(tmem_base, da[0], db[0], idesc, (g > 0 || u > 0) ? 1u : 0u);
+          umma_ss(tmem_base, da[0], db[1], idesc, 1u);
+          umma_ss(tmem_base, da[1], db[0], idesc, 1u);
+          umma_ss(tmem_base, da[0], db[2], idesc, 1u);
+          umma_ss(tmem_base, da[1], db[1], idesc, 1u);
+          umma_ss(tmem_base, da[2], db[0], idesc, 1u);
+        }
+        umma_commit(op_empty + 8 * os);
+      }
+      umma_commit(acc_full);
+    }
+    __syncwarp();
+  } else {
+    // ---- converters: warps 4-11 dY, 12-19 X; lane -> (sample, 16-byte column) as in gemm_ws_kernel: conflict-free both ways ----
+    const int ct = tid - 128, opnd = ct >> 8, c = ct & 255;
+    for (int g = 0; g < n_slab; ++g) {
+      const uint32_t rs = g % WW_STAGES, os = g & 1;
+      mbar_wait((opnd ? rawb_full : rawa_full) + 8 * rs, (g / WW_STAGES) & 1);
+      mbar_wait(op_empty + 8 * os, ((g >> 1) & 1) ^ 1);
+      const uint32_t raw = sbase + rs * 2 * WW_RAW + opnd * WW_RAW;
+      const uint32_t base = sbase + WW_OFF_OP + os * 2 * TC_OPER + opnd * TC_OPER;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int pl = (c & 7) | (q << 3), c4 = ((c >> 3) & 1) | (((c >> 4) & 15) << 1);
+        const uint4 v = lds128(raw + pl * 512 + ((c4 ^ (pl & 7)) << 4));
+        uint32_t w0[3], w1[3];
+        split3(__uint_as_float(v.x), __uint_as_float(v.y), w0);
+        split3(__uint_as_float(v.z), __uint_as_float(v.w), w1);
+        const uint32_t addr = base + q * TC_CHUNK + (c4 >> 1) * 128 + (pl & 7) * 16 + (c4 & 1) * 8;
+#pragma unroll
+        for (int pt = 0; pt < TC_PARTS; ++pt)
+          asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr + pt * TC_PART), "r"(w0[pt]), "r"(w1[pt]) : "memory");
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) { mbar_arrive(op_full + 8 * os); mbar_arrive(raw_empty + 8 * rs); }
+    }
+    // ---- epilogue: warp (4 + 4b + q) owns TMEM lanes 32q.. and columns 32b..: transpose through the (now idle) raw ring and
+    // add the 32 x 32 block to dW with one coalesced 128-byte atomic row per instruction ------------------------------------------
+    if (n_slab > 0) {
+      const int q = warp & 3, b = (warp - 4) >> 2;
+      mbar_wait_backoff(acc_full, 0);
+      tc_fence_after();
+      uint32_t acc[32];
+      tmem_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + 32 * b, acc);
+      tmem_wait_ld();
+      float *tile = reinterpret_cast<float *>(ww_smem) + (warp - 4) * (32 * 33);
+#pragma unroll
+      for (int k = 0; k < 32; ++k) tile[lane * 33 + k] = __uint_as_float(acc[k]);
+      __syncwarp();
+      const int j = j0 + 32 * b + lane;
+      if (j < J) {
+        const int nrow = min(32, I - (i0 + 32 * q));
+        float *dst = C + (long long)(i0 + 32 * q) * ldc + j;
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r)
+          if (r < nrow) atomicAdd(dst + (long long)r * ldc, tile[r * 33 + lane]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 3) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+  }
+}
+
 // ---- the 3- and 1-wide heads (confi_rgb / alpha_1 / rgb / alpha, network/models.py:161-162,170,174) ------------------
 // A 64- or 128-wide GEMM tile would be >95 % padding there; these three kernels stream the wide operand once, coalesced.
 // forward: warp per row, lanes over k, shuffle reduction.  Y[m][n] (+)= sum_k X[m][k] W[n][k] + b[n], N <= 4
@@ -1093,8 +1283,31 @@ extern "C" int ucn_linear_bwd_weight(const float *dY, int64_t ldy, const float *
   int splits = (int)((2 * ucn_sm_count() + tiles - 1) / tiles);
   const long long max_splits = (M + 255) / 256;
   if (splits > max_splits) splits = (int)max_splits;
-  if (g_gemm_dbg >> 8) splits = g_gemm_dbg >> 8;      // timing switch (tools/ubench_gemm.py)
-  const int rc = launch_gemm(dY, 1, ldy, X, ldx, 1, dW, lddw, nullptr, N, K, M, G_ATOMIC, splits < 1 ? 1 : splits, stream);
+  if (g_gemm_dbg >> 12) splits = g_gemm_dbg >> 12;    // timing switch (tools/ubench_gemm.py)
+  int rc;
+  // long reductions over 16-byte-aligned dY rows: the MN-major pipeline (X may have any row pitch: 4-byte copies then)
+  // (measured: with 4-byte copies of an unaligned X the pipeline is SLOWER than gemm_tc_kernel, 279 vs 195 us at K = 191 --
+  // those products, K2's 61-float feature rows in this path, stay on the old kernel unless the debug flag 256 forces them here)
+  const bool x_vec = (reinterpret_cast<uintptr_t>(X) & 15) == 0 && (ldx & 3) == 0;
+  if (tc && M >= 4096 && !(g_gemm_dbg & 128) && (x_vec || (g_gemm_dbg & 256)) && (reinterpret_cast<uintptr_t>(dY) & 15) == 0 && (ldy & 3) == 0) {
+    static int attr_w[kUcnMaxDevices], attr_w2[kUcnMaxDevices];
+    cudaError_t e = x_vec ? ucn_ensure_dyn_smem(gemm_wsw_kernel<true>, (int)WW_SMEM, attr_w)
+                          : ucn_ensure_dyn_smem(gemm_wsw_kernel<false>, (int)WW_SMEM, attr_w2);
+    if (e != cudaSuccess) return ucn_cuda_status(e, "gemm_wsw smem attribute");
+    const long long n_slab = (M + TC_SLAB - 1) / TC_SLAB;
+    long long ctas = ucn_sm_count() / tiles;
+    if (ctas < 1) ctas = 1;
+    const int per = (int)((n_slab + ctas - 1) / ctas);
+    dim3 grid((unsigned)((n_slab + per - 1) / per), (unsigned)tiles);
+    if (x_vec)
+      gemm_wsw_kernel<true><<<grid, WS_THREADS, WW_SMEM, (cudaStream_t)stream>>>(dY, ldy, X, ldx, dW, lddw, N, K, M, per);
+    else
+      gemm_wsw_kernel<false><<<grid, WS_THREADS, WW_SMEM, (cudaStream_t)stream>>>(dY, ldy, X, ldx, dW, lddw, N, K, M, per);
+    UCN_LAUNCH_CHECK("gemm_wsw_kernel");
+    rc = UCN_OK;
+  } else {
+    rc = launch_gemm(dY, 1, ldy, X, ldx, 1, dW, lddw, nullptr, N, K, M, G_ATOMIC, splits < 1 ? 1 : splits, stream);
+  }
   if (rc != UCN_OK || !db) return rc;
   const long long chunks = (M + 511) / 512;
   colsum_kernel<<<dim3(nblk(N, 32), (unsigned)chunks), 256, 0, (cudaStream_t)stream>>>(dY, ldy, M, N, 512, db);
