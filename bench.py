@@ -219,7 +219,22 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
     flag = torch.zeros(1, device=dev)
     ren_box, bar_ev, host_submit = {}, [], {}
 
+    # Peer mode: the per-frame barrier runs on a side stream.  Frame i's barrier (every rank's tile is in the root's buffer
+    # i&1) is needed before the root reads that buffer and before any rank's K4 of frame i+2 overwrites it -- not before
+    # frame i+1 starts: taking it off the main stream stops every frame from waiting for that frame's slowest rank
+    # (ranks differ by 4-5 % and jitter; the frame period becomes the ranks' average, not the per-frame maximum).
+    side = torch.cuda.Stream(device=dev) if (peer_mode and args.barrier == "side") else None
+    done = [None, None]
+    flags2 = [torch.zeros(1, device=dev) for _ in range(2)]
+
+    def drain():
+        for d in done:
+            if d is not None:
+                torch.cuda.current_stream().wait_event(d)
+
     def step_resident(timers, seed, i=0):
+        if side is not None and done[i & 1] is not None:
+            torch.cuda.current_stream().wait_event(done[i & 1])      # buffer i&1: frame i-2 is complete (and consumed)
         fr = pack(resident)
         ren = ren_box.get("r")
         if ren is None:
@@ -229,6 +244,19 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
         ren.render(ray0, n_tile, seed=seed, out_rgb=out[0], out_depth=out[1], timers=timers)
         if split:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if side is not None:
+                ev = torch.cuda.Event()
+                ev.record()
+                with torch.cuda.stream(side):
+                    side.wait_event(ev)
+                    e0.record(side)
+                    dist.all_reduce(flags2[i & 1])      # frame complete on the root once this returns in stream order
+                    e1.record(side)
+                    d = torch.cuda.Event()
+                    d.record(side)
+                    done[i & 1] = d
+                bar_ev.append((e0, e1))
+                return
             e0.record()
             if peer_mode:
                 dist.all_reduce(flag)                   # frame complete on the root once this returns in stream order
@@ -260,6 +288,7 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
         e0.record()
         for i in range(n):
             fn(i)
+        drain()                                          # the last frames' barriers (side stream) are part of the work
         e1.record()
         submit = (time.perf_counter() - t0) * 1e3        # host time to SUBMIT the n steps (no synchronisation inside)
         barrier()
@@ -367,7 +396,9 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
         if split:
             par = (f"one frame as {world} contiguous row tiles (shard.row_tile), "
                    + ("K4 peer-stores each tile into the root's frame buffer over NVLink (16 B/ray), one 4-byte all-reduce per "
-                      "frame as barrier, root reads the frame out" if peer_mode else "ncclAllGather of [R/P,4] tiles")
+                      "frame as barrier" + (" on a side stream (it gates the root's read-out and frame i+2's stores into the "
+                                            "same buffer, not the start of frame i+1)" if args.barrier == "side" else " in line")
+                      + ", root reads the frame out" if peer_mode else "ncclAllGather of [R/P,4] tiles")
                    + "; every rank packs only its row band of the target-frustum maps")
         elif world > 1:
             par = f"replicas x{world}: one whole view per rank, no data-path collective"
@@ -489,6 +520,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N>1: image gather by K4 peer stores into the root's frame buffer (default) or ncclAllGather")
+    ap.add_argument("--barrier", default="side", choices=("side", "inline"),
+                    help="N>1 peer mode: per-frame barrier on a side stream (default) or in line on the render stream")
     ap.add_argument("--replicas", action="store_true", help="N>1: one whole view per rank (round-1 weak-scaling measurement)")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra blocks (config 5 full box, config 4, replicas, eager)")
     args = ap.parse_args()
