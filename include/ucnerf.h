@@ -290,6 +290,12 @@ int ucn_cost_volume_variance(const float *feats, int V, int C, int H, int W, con
 size_t ucn_metrics_workspace_bytes(void);
 /* *out_sum += sum (a[i]-b[i])^2;  PSNR = -10 log10(sum / n) */
 int ucn_sq_err_sum(const float *a, const float *b, int64_t n, double *out_sum, void *stream);
+/* SSIM as the reference's rgb_evaluation takes it (utils/evaluation.py:93: skimage.metrics.structural_similarity with
+ * data_range = 1 and the library's defaults -- scikit-image >= 0.21 per requirements.txt:8, not vendored: 7 x 7 uniform
+ * window, sample covariance, K1 = 0.01, K2 = 0.03, mean over the map cropped by 3 pixels, then over channels).
+ * a, b [C][H][W] fp32; *out_sum += the sum of the SSIM map over channels and interior pixels (fp64; caller zeroes it);
+ * mean SSIM = sum / (C (H-6) (W-6)). */
+int ucn_ssim_sum(const float *a, const float *b, int C, int H, int W, float data_range, double *out_sum, void *stream);
 /* exact medians of valid gt / pred depths (valid: min_depth < gt < max_depth and mask != 0, mask may be NULL):
  * out_mid4 = {gt, gt, pred, pred} values of ranks (c-1)/2 and c/2 (numpy's median is their mean), *out_count = c */
 int ucn_depth_median(const float *gt, const float *pred, const unsigned char *mask, int64_t n, float min_depth,

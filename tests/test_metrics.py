@@ -108,3 +108,59 @@ def test_cuda_metrics_full_frame_properties():
     assert abs(ps[0] - (-20 * np.log10(0.125))) < 1e-4
     with pytest.raises(Exception):
         M.get_psnr([rgb.cpu()], [rgb.cpu()])                            # no CPU path
+
+
+def _ssim_brute(a, b, data_range=1.0):
+    """The SSIM definition evaluated window by window (loops, float64): the pin of oracle.metrics.ssim."""
+    c1, c2 = (0.01 * data_range) ** 2, (0.03 * data_range) ** 2
+    vals = []
+    for p, q in zip(np.asarray(a, np.float64), np.asarray(b, np.float64)):
+        H, W = p.shape
+        s = []
+        for y in range(3, H - 3):
+            for x in range(3, W - 3):
+                wp, wq = p[y - 3:y + 4, x - 3:x + 4].ravel(), q[y - 3:y + 4, x - 3:x + 4].ravel()
+                up, uq = wp.mean(), wq.mean()
+                vp, vq = wp.var(ddof=1), wq.var(ddof=1)
+                vpq = ((wp - up) * (wq - uq)).sum() / 48.0
+                s.append(((2 * up * uq + c1) * (2 * vpq + c2)) / ((up * up + uq * uq + c1) * (vp + vq + c2)))
+        vals.append(np.mean(s))
+    return float(np.mean(vals))
+
+
+def _ssim_images(seed, C, H, W):
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:H, 0:W]
+    base = 0.5 + 0.4 * np.sin(0.21 * xx + 0.13 * yy)[None] * np.cos(0.05 * xx * np.arange(1, C + 1)[:, None, None])
+    gt = np.clip(base + 0.02 * rng.standard_normal((C, H, W)), 0, 1).astype(np.float32)
+    pred = np.clip(gt + 0.08 * rng.standard_normal((C, H, W)), 0, 1).astype(np.float32)
+    return gt, pred
+
+
+def test_oracle_ssim_matches_the_definition():
+    """skimage is neither vendored in the reference nor installed here: the restatement is pinned to the published
+    formula evaluated window by window, and to the identities SSIM(x, x) = 1 and symmetry."""
+    for seed, (C, H, W) in enumerate(((3, 12, 17), (1, 7, 7), (3, 20, 9))):
+        gt, pred = _ssim_images(seed, C, H, W)
+        assert abs(OM.ssim(gt, pred) - _ssim_brute(gt, pred)) <= 1e-12
+        assert abs(OM.ssim(gt, gt) - 1.0) <= 1e-12
+        assert abs(OM.ssim(gt, pred) - OM.ssim(pred, gt)) <= 1e-12
+    gt, pred = _ssim_images(9, 3, 16, 16)
+    assert 0.0 < OM.ssim(gt, pred) < 0.999
+
+
+@pytest.mark.gpu
+def test_cuda_ssim_matches_oracle():
+    import torch
+    from ucnerf_b200 import metrics as M
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    for seed, (C, H, W) in enumerate(((3, 12, 17), (1, 7, 7), (3, 64, 80), (3, 41, 39), (3, 512, 640))):
+        gt, pred = _ssim_images(seed, C, H, W)
+        got = M.ssim(T(gt), T(pred))
+        assert got.shape == (1,) and abs(got[0] - OM.ssim(gt, pred)) <= 1e-9, (C, H, W, got)
+    gts = np.stack([_ssim_images(20 + i, 3, 32, 48)[0] for i in range(3)])
+    preds = np.stack([_ssim_images(20 + i, 3, 32, 48)[1] for i in range(3)])
+    got = M.ssim(T(gts), T(preds))
+    want = [OM.ssim(g, p) for g, p in zip(gts, preds)]
+    assert np.abs(got - np.array(want)).max() <= 1e-9
+    assert abs(M.ssim(T(gts), T(gts)).max() - 1.0) <= 1e-12

@@ -140,6 +140,55 @@ depth_err_kernel(const float *__restrict__ gt, const float *__restrict__ pred, c
   block_sum_to(s, 8, out8);
 }
 
+// SSIM map of one channel plane, summed over the interior (utils/evaluation.py:93 calls
+// skimage.metrics.structural_similarity(gt, pred, data_range=1, channel_axis=2) with its defaults: 7 x 7 uniform window,
+// sample covariance (x 49/48), K1 = 0.01, K2 = 0.03, the mean taken over the map cropped by 3 pixels per side, then over
+// the channels).  Block = 32 x 8 output pixels of one plane; the (32+6) x (8+6) input patch of both images goes through
+// shared memory, the 7 x 7 sums are taken in fp64.
+constexpr int SS_W = 32, SS_H = 8, SS_R = 3;
+__global__ void __launch_bounds__(SS_W * SS_H)
+ssim_kernel(const float *__restrict__ a, const float *__restrict__ b, int H, int W, double c1, double c2,
+            double *__restrict__ out_sum) {
+  __shared__ float sa[SS_H + 2 * SS_R][SS_W + 2 * SS_R], sb[SS_H + 2 * SS_R][SS_W + 2 * SS_R];
+  __shared__ double red[SS_W * SS_H / 32];
+  const float *pa = a + (size_t)blockIdx.z * H * W, *pb = b + (size_t)blockIdx.z * H * W;
+  const int x0 = SS_R + blockIdx.x * SS_W, y0 = SS_R + blockIdx.y * SS_H;      // first interior pixel of the tile
+  for (int i = threadIdx.x; i < (SS_H + 2 * SS_R) * (SS_W + 2 * SS_R); i += SS_W * SS_H) {
+    const int ly = i / (SS_W + 2 * SS_R), lx = i % (SS_W + 2 * SS_R);
+    const int y = y0 - SS_R + ly, x = x0 - SS_R + lx;
+    const bool ok = y < H && x < W;
+    sa[ly][lx] = ok ? pa[(size_t)y * W + x] : 0.f;
+    sb[ly][lx] = ok ? pb[(size_t)y * W + x] : 0.f;
+  }
+  __syncthreads();
+  const int tx = threadIdx.x % SS_W, ty = threadIdx.x / SS_W;
+  const int x = x0 + tx, y = y0 + ty;
+  double s = 0.0;
+  if (x < W - SS_R && y < H - SS_R) {
+    double ua = 0, ub = 0, uaa = 0, ubb = 0, uab = 0;
+#pragma unroll
+    for (int dy = 0; dy < 2 * SS_R + 1; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2 * SS_R + 1; ++dx) {
+        const double p = sa[ty + dy][tx + dx], q = sb[ty + dy][tx + dx];
+        ua += p; ub += q; uaa += p * p; ubb += q * q; uab += p * q;
+      }
+    const double np_ = 49.0, cov = np_ / (np_ - 1.0);
+    ua /= np_; ub /= np_; uaa /= np_; ubb /= np_; uab /= np_;
+    const double va = cov * (uaa - ua * ua), vb = cov * (ubb - ub * ub), vab = cov * (uab - ua * ub);
+    s = ((2.0 * ua * ub + c1) * (2.0 * vab + c2)) / ((ua * ua + ub * ub + c1) * (va + vb + c2));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < SS_W * SS_H / 32; ++i) t += red[i];
+    atomicAdd(out_sum, t);
+  }
+}
+
 inline unsigned grid_for(long long n) {
   const long long b = (n + kThreads - 1) / kThreads;
   const long long cap = 8ll * ucn_sm_count();                      // persistent grid-stride: 8 CTAs per SM
@@ -156,6 +205,20 @@ extern "C" int ucn_sq_err_sum(const float *a, const float *b, int64_t n, double 
   if (n <= 0) return UCN_OK;
   sq_err_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(a, b, n, out_sum);
   UCN_LAUNCH_CHECK("sq_err_kernel");
+  return UCN_OK;
+}
+
+// *out_sum += sum over the C channel planes and the interior pixels (3 .. H-4, 3 .. W-4) of the SSIM map of a vs b
+// ([C][H][W] fp32, data_range = 1 scaled by `data_range`); mean SSIM = sum / (C (H-6) (W-6)).  The caller zeroes out_sum.
+extern "C" int ucn_ssim_sum(const float *a, const float *b, int C, int H, int W, float data_range, double *out_sum,
+                            void *stream) {
+  UCN_CHECK_ARG(a && b && out_sum, "ucn_ssim_sum: null argument");
+  UCN_CHECK_ARG(C >= 1 && C <= 65535 && H >= 7 && W >= 7, "ucn_ssim_sum: the 7 x 7 window needs images of at least 7 x 7 pixels");
+  const double c1 = (0.01 * data_range) * (0.01 * data_range), c2 = (0.03 * data_range) * (0.03 * data_range);
+  dim3 grid((unsigned)((W - 2 * SS_R + SS_W - 1) / SS_W), (unsigned)((H - 2 * SS_R + SS_H - 1) / SS_H), (unsigned)C);
+  UCN_CHECK_ARG(grid.y < 65536u, "ucn_ssim_sum: image too tall");
+  ssim_kernel<<<grid, SS_W * SS_H, 0, (cudaStream_t)stream>>>(a, b, H, W, c1, c2, out_sum);
+  UCN_LAUNCH_CHECK("ssim_kernel");
   return UCN_OK;
 }
 

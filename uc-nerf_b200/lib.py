@@ -109,6 +109,7 @@ _SIGS = {
                                            _fp, _fp]),
     "ucn_metrics_workspace_bytes": (C.c_size_t, []),
     "ucn_sq_err_sum": (C.c_int, [_fp, _fp, C.c_int64, _fp, _fp]),
+    "ucn_ssim_sum": (C.c_int, [_fp, _fp, C.c_int, C.c_int, C.c_int, C.c_float, _fp, _fp]),
     "ucn_depth_median": (C.c_int, [_fp, _fp, _fp, C.c_int64, C.c_float, C.c_float, _fp, C.c_size_t, _fp, _fp, _fp]),
     "ucn_depth_errors": (C.c_int, [_fp, _fp, _fp, C.c_int64, C.c_float, C.c_float, C.c_float, _fp, _fp]),
     "ucn_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),

@@ -46,6 +46,25 @@ def get_psnr(imgs_pred: Sequence[torch.Tensor], imgs_gt: Sequence[torch.Tensor])
     return -10.0 * np.log(mse) / np.log(10.0)
 
 
+def ssim(gts: torch.Tensor, predicts: torch.Tensor, data_range: float = 1.0) -> np.ndarray:
+    """Per-image SSIM of [N,C,H,W] (or [C,H,W]) images in [0, data_range] -> float64 array [N]: what
+    utils/evaluation.py:88-95 computes with skimage.metrics.structural_similarity(gt, pred, data_range=1,
+    channel_axis=2) (7 x 7 uniform window, sample covariance, mean of the map cropped by 3 pixels, mean over channels),
+    on the GPU; one device->host copy for the whole batch."""
+    lib = L.load()
+    a, b = _f32(gts), _f32(predicts)
+    if a.dim() == 3:
+        a, b = a[None], b[None]
+    if a.shape != b.shape or a.dim() != 4:
+        raise ValueError("ssim: expected two [N,C,H,W] (or [C,H,W]) tensors of the same shape")
+    N, Cn, H, W = a.shape
+    sums = torch.zeros(N, dtype=torch.float64, device=a.device)
+    for i in range(N):
+        L.check(lib.ucn_ssim_sum(L.ptr(a[i]), L.ptr(b[i]), Cn, H, W, float(data_range), C.c_void_p(sums[i:].data_ptr()),
+                                 L.stream_ptr()), "ucn_ssim_sum")
+    return sums.cpu().numpy() / float(Cn * (H - 6) * (W - 6))
+
+
 def _errors_from_sums(s: np.ndarray):
     c = s[7]
     return (s[0] / c, s[1] / c, float(np.sqrt(s[2] / c)), float(np.sqrt(s[3] / c)), s[4] / c, s[5] / c, s[6] / c)
