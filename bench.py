@@ -520,8 +520,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N>1: image gather by K4 peer stores into the root's frame buffer (default) or ncclAllGather")
-    ap.add_argument("--barrier", default="side", choices=("side", "inline"),
-                    help="N>1 peer mode: per-frame barrier on a side stream (default) or in line on the render stream")
+    ap.add_argument("--barrier", default="inline", choices=("side", "inline"),
+                    help="N>1 peer mode: per-frame barrier in line on the render stream (default) or on a side stream "
+                         "(1-2 %% faster at N = 8 when it works, but a resident NCCL kernel can keep one CTA of the persistent "
+                         "MLP kernel off its SM: one 2-GPU run fell to 130 ms per frame -- experimental)")
     ap.add_argument("--replicas", action="store_true", help="N>1: one whole view per rank (round-1 weak-scaling measurement)")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra blocks (config 5 full box, config 4, replicas, eager)")
     args = ap.parse_args()
