@@ -560,7 +560,7 @@ def main():
         r = bench_train.measure(targs, ClockSampler, peaks, ctx, full=False)
         if r:
             extra["train_c4"] = {k: r.get(k) for k in ("value", "ms_per_step", "scaling", "config", "e2e", "gpu_launches",
-                                                        "kernels_ms_per_step", "roofline", "loss_first_last")}
+                                                        "kernels_ms_per_step", "roofline", "loss_first_last", "parity")}
         if world == 1 and rank == 0:
             try:
                 extra["gpu_eager_baseline"] = gpu_eager_baseline(args.workload, dev)
