@@ -140,7 +140,10 @@ __device__ __forceinline__ void touch(const float *p) {
 // C0 is a template parameter so that the head weights are immediate-offset constant-bank operands of the FFMAs (no
 // load instruction: the 4-wide heads were 256 broadcast LDS.128 per thread and round through the shared-memory pipe).
 // (C0 < 0: the chunk offset is the runtime argument `c0r` -- one instantiation per mode keeps the code in the I-cache.)
-template <int MODE, bool HEADS, int C0>
+// HM: which of the four head outputs this chunk's columns feed (bit k = output k).  The adapt heads are block-structured --
+// rgb reads columns 0..63 of the view hidden, alpha columns 64..127 (models.py:170,174) -- so half of their 512 products per row
+// are multiplications by the zero blocks of [[W_rgb, 0], [0, W_alpha]]: skipping them is bit-identical (x * 0 + acc == acc).
+template <int MODE, bool HEADS, int C0, int HM = 15>
 __device__ __forceinline__ void epi32(uint32_t t_d, uint32_t t_other, const float *__restrict__ bias,
                                       const float *__restrict__ rayb, uint32_t mod_row, const float (&w4)[512],
                                       float (&head)[4], int c0r = 0) {
@@ -188,8 +191,10 @@ __device__ __forceinline__ void epi32(uint32_t t_d, uint32_t t_other, const floa
       if (HEADS) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          head[0] = fmaf(v[8 * j + i], w4[4 * (c + i)], head[0]); head[1] = fmaf(v[8 * j + i], w4[4 * (c + i) + 1], head[1]);
-          head[2] = fmaf(v[8 * j + i], w4[4 * (c + i) + 2], head[2]); head[3] = fmaf(v[8 * j + i], w4[4 * (c + i) + 3], head[3]);
+          if (HM & 1) head[0] = fmaf(v[8 * j + i], w4[4 * (c + i)], head[0]);
+          if (HM & 2) head[1] = fmaf(v[8 * j + i], w4[4 * (c + i) + 1], head[1]);
+          if (HM & 4) head[2] = fmaf(v[8 * j + i], w4[4 * (c + i) + 2], head[2]);
+          if (HM & 8) head[3] = fmaf(v[8 * j + i], w4[4 * (c + i) + 3], head[3]);
         }
       }
     }
@@ -623,7 +628,16 @@ mlp_x3p_kernel(const __grid_constant__ Plan plan, const __grid_constant__ HeadW 
           if (has_next) { __syncwarp(); if (lane == 0) mbar_arrive(goA); }
           head[0] = head[1] = head[2] = head[3] = 0.f;
           const float *rb = rayb_s + (s * rpt + cur.ri) * 128;
-          EPI_PAIR(2, true, t_P, 0, f32s + ucn::X3Layout::b_vv, rb, hw.adapt, false);
+          {
+            const float *bvv = f32s + ucn::X3Layout::b_vv;
+            if (hf == 0) {
+              epi32<2, true, 0, 7>(t_P, 0, bvv, rb, mod_row, hw.adapt, head);
+              epi32<2, true, 64, 8>(t_P, 0, bvv, rb, mod_row, hw.adapt, head);
+            } else {
+              epi32<2, true, 32, 7>(t_P, 0, bvv, rb, mod_row, hw.adapt, head);
+              epi32<2, true, 96, 8>(t_P, 0, bvv, rb, mod_row, hw.adapt, head);
+            }
+          }
           if (has_next) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(goB); }
           if (hf == 1) {
             exch_s[s * 128 + row] = make_float4(head[0], head[1], head[2], head[3]);
