@@ -299,15 +299,19 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
         host_submit["ms"] = ms[2].item() / n
         return ms[0].item() / n, ms[1].item() / n
 
+    # nvidia-smi is started BEFORE the warm-up: its start-up (NVML initialisation, first driver queries) has been seen to
+    # stall kernel launches for ~0.4 s, which is most of a 5-step timed region (two runs at 124-130 ms per frame); its
+    # samples then cover warm-up + timed region, both under load
+    sampler = ClockSampler(local) if full else None
+    if rank == 0 and sampler:
+        sampler.start()
+        time.sleep(0.5)
     for i in range(warmup):
         step_resident(None, 1000 + i, i)
     do_e2e = peer_mode or not split
     if do_e2e:
         for i in range(max(2, warmup // 2)):
             step_e2e(i, max(2, warmup // 2))
-    sampler = ClockSampler(local) if full else None
-    if rank == 0 and sampler:
-        sampler.start()
     # timed region: the fused call (ucn_render_rays), as a user runs it.  The per-kernel breakdown (roofline) comes from an
     # instrumented pass of the same K steps right after it, still under the clock sampler: CUDA events between the kernels
     # cost the frame 3-4 % (no back-to-back launches), which is why they are kept out of `value`.

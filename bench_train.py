@@ -203,12 +203,13 @@ def measure(args, ClockSampler, peaks, ctx, full=True):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms[0].item() / steps, ms[1].item() / steps
 
+    sampler = ClockSampler(local) if full else None      # started before the warm-up: see bench.measure_render
+    if rank == 0 and sampler:
+        sampler.start()
+        time.sleep(0.5)
     for i in range(max(3, args.warmup)):
         step(i, read_loss=True)
     loss0 = box["loss"]
-    sampler = ClockSampler(local) if full else None
-    if rank == 0 and sampler:
-        sampler.start()
     timers = []
     L.launch_count(reset=True)
     ms, wall_ms = timed(lambda i: step(100 + i, timers), args.steps)

@@ -120,6 +120,31 @@ __device__ __forceinline__ void pos_enc(const float (&x)[3], float *pe) {
   }
 }
 
+// sm_100 packed fp32 arithmetic: two IEEE round-to-nearest operations per instruction (same results as the scalar forms)
+__device__ __forceinline__ void add2_f32(float &x0, float &x1, float b0, float b1) {
+  asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %3};\n\tadd.rn.f32x2 a, a, b;\n\tmov.b64 {%0, %1}, a;\n\t}"
+      : "+f"(x0), "+f"(x1) : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void mul2_f32(float &x0, float &x1, float b0, float b1) {
+  asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %3};\n\tmul.rn.f32x2 a, a, b;\n\tmov.b64 {%0, %1}, a;\n\t}"
+      : "+f"(x0), "+f"(x1) : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void sub2_f32(float &x0, float &x1, float b0, float b1) {
+  asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %3};\n\tsub.rn.f32x2 a, a, b;\n\tmov.b64 {%0, %1}, a;\n\t}"
+      : "+f"(x0), "+f"(x1) : "f"(b0), "f"(b1));
+}
+// (a0, a1) += v * (w0, w1): one FFMA2 (the scalar operand is broadcast, the weight pair comes from a uniform register)
+__device__ __forceinline__ void fma2_bcast(float &a0, float &a1, float v, float w0, float w1) {
+  asm("{\n\t.reg .b64 a, b, c;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %2};\n\tmov.b64 c, {%3, %4};\n\tfma.rn.f32x2 a, b, c, a;\n\tmov.b64 {%0, %1}, a;\n\t}"
+      : "+f"(a0), "+f"(a1) : "f"(v), "f"(w0), "f"(w1));
+}
+// split2 with the two residual subtractions as one packed instruction
+__device__ __forceinline__ void split2p(float a, float b, uint32_t &hi, uint32_t &lo) {
+  hi = pack2(a, b);
+  sub2_f32(a, b, bf_lo(hi), bf_hi(hi));
+  lo = pack2(a, b);
+}
+
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
@@ -164,8 +189,10 @@ __device__ __forceinline__ void epi32(uint32_t t_d, uint32_t t_other, const floa
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const uint32_t wh = hq[16 * u + 4 * j + i], wl = hq[16 * u + 8 + 4 * j + i];
-          v[8 * j + 2 * i] = (bf_lo(wh) + bf_lo(wl)) * __uint_as_float(a[16 * u + 8 * j + 2 * i]);
-          v[8 * j + 2 * i + 1] = (bf_hi(wh) + bf_hi(wl)) * __uint_as_float(a[16 * u + 8 * j + 2 * i + 1]);
+          float h0 = bf_lo(wh), h1 = bf_hi(wh);
+          add2_f32(h0, h1, bf_lo(wl), bf_hi(wl));
+          mul2_f32(h0, h1, __uint_as_float(a[16 * u + 8 * j + 2 * i]), __uint_as_float(a[16 * u + 8 * j + 2 * i + 1]));
+          v[8 * j + 2 * i] = h0; v[8 * j + 2 * i + 1] = h1;
         }
       } else {
         const float4 b0 = *reinterpret_cast<const float4 *>(bias + c), b1 = *reinterpret_cast<const float4 *>(bias + c + 4);
@@ -181,26 +208,33 @@ __device__ __forceinline__ void epi32(uint32_t t_d, uint32_t t_other, const floa
           rb[0] = r0.x; rb[1] = r0.y; rb[2] = r0.z; rb[3] = r0.w; rb[4] = r1.x; rb[5] = r1.y; rb[6] = r1.z; rb[7] = r1.w;
         }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float x = __uint_as_float(a[16 * u + 8 * j + i]) + bb[i];
-          if (MODE == 0) v[8 * j + i] = fmaxf(x * mm[i], 0.0f);
-          if (MODE == 1) v[8 * j + i] = x;
-          if (MODE == 2) v[8 * j + i] = fmaxf(x + rb[i], 0.0f);
+        for (int i = 0; i < 8; i += 2) {
+          float x0 = __uint_as_float(a[16 * u + 8 * j + i]), x1 = __uint_as_float(a[16 * u + 8 * j + i + 1]);
+          add2_f32(x0, x1, bb[i], bb[i + 1]);
+          if (MODE == 0) { mul2_f32(x0, x1, mm[i], mm[i + 1]); x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
+          if (MODE == 2) { add2_f32(x0, x1, rb[i], rb[i + 1]); x0 = fmaxf(x0, 0.0f); x1 = fmaxf(x1, 0.0f); }
+          v[8 * j + i] = x0; v[8 * j + i + 1] = x1;
         }
       }
       if (HEADS) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          if (HM & 1) head[0] = fmaf(v[8 * j + i], w4[4 * (c + i)], head[0]);
-          if (HM & 2) head[1] = fmaf(v[8 * j + i], w4[4 * (c + i) + 1], head[1]);
-          if (HM & 4) head[2] = fmaf(v[8 * j + i], w4[4 * (c + i) + 2], head[2]);
-          if (HM & 8) head[3] = fmaf(v[8 * j + i], w4[4 * (c + i) + 3], head[3]);
+          if ((HM & 3) == 3) fma2_bcast(head[0], head[1], v[8 * j + i], w4[4 * (c + i)], w4[4 * (c + i) + 1]);
+          else {
+            if (HM & 1) head[0] = fmaf(v[8 * j + i], w4[4 * (c + i)], head[0]);
+            if (HM & 2) head[1] = fmaf(v[8 * j + i], w4[4 * (c + i) + 1], head[1]);
+          }
+          if ((HM & 12) == 12) fma2_bcast(head[2], head[3], v[8 * j + i], w4[4 * (c + i) + 2], w4[4 * (c + i) + 3]);
+          else {
+            if (HM & 4) head[2] = fmaf(v[8 * j + i], w4[4 * (c + i) + 2], head[2]);
+            if (HM & 8) head[3] = fmaf(v[8 * j + i], w4[4 * (c + i) + 3], head[3]);
+          }
         }
       }
     }
     if (MODE != 2) {                                       // the unit's accumulator words are dead: reuse them for the operand
 #pragma unroll
-      for (int i = 0; i < 8; ++i) split2(v[2 * i], v[2 * i + 1], a[16 * u + i], a[16 * u + 8 + i]);
+      for (int i = 0; i < 8; ++i) split2p(v[2 * i], v[2 * i + 1], a[16 * u + i], a[16 * u + 8 + i]);
     }
   }
   if (MODE != 2) tmem_st32(t_d + c0, a);                   // one 4 KB store per warp and chunk
