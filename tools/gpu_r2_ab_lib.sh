@@ -1,5 +1,7 @@
 #!/bin/bash
-# same-box A/B of two builds of libucnerf.so (tools/ab/libucnerf_{old,new}.so) on the K3 microbenchmark
+# same-box A/B of two builds of libucnerf.so on the K3 microbenchmark.  Prepare here first (the .so files are git-ignored but
+# travel with gpurun):  build the new tree, cp uc-nerf_b200/libucnerf.so tools/ab/libucnerf_new.so;  git stash, build,
+# cp ... tools/ab/libucnerf_old.so;  git stash pop, rebuild.  Read the MIN column: the median moves with the clock ramp.
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 for v in old new old new; do
