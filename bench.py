@@ -70,7 +70,13 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        self.idx, self.proc, self.path = gpu_index, None, f"/tmp/ucnerf_clocks_{os.getpid()}.csv"
+        self.idx, self.proc, self.path, self.off = gpu_index, None, f"/tmp/ucnerf_clocks_{os.getpid()}.csv", 0
+
+    def mark(self):
+        try:
+            self.off = os.path.getsize(self.path)
+        except OSError:
+            self.off = 0
 
     def start(self):
         try:
@@ -87,7 +93,9 @@ class ClockSampler:
         self.proc.terminate()
         self.proc.wait()
         sm, mx, reasons = [], [], set()
-        for line in open(self.path):
+        fh = open(self.path)
+        fh.seek(self.off)
+        for line in fh:
             f = [x.strip() for x in line.split(",")]
             if len(f) < 9:
                 continue
@@ -102,6 +110,74 @@ class ClockSampler:
         busy = sorted(sm)[len(sm) // 2:] if sm else []
         return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class NvmlClockSampler:
+    """The same quantities through NVML in this process (a thread polling every 200 ms): SM clock, max SM clock and the
+    throttle-reason bit mask.  `nvidia-smi -lms` polling the recipe's nine fields (power.draw among them) during the timed
+    region was measured to slow the timed region itself down -- 37.7 -> 49.2 ms per frame with host submission going from
+    0.6 to 12 ms per frame -- so it is the fallback (UCN_CLOCKS=smi), not the default."""
+    REASONS = {0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown", 0x8: "hw_slowdown", 0x4: "sw_power_cap"}
+
+    def __init__(self, gpu_index):
+        self.idx, self.thread, self.samples, self.stop_flag, self.mx, self.t_mark = gpu_index, None, [], False, None, 0.0
+
+    def start(self):
+        import threading
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.idx]) if vis and vis.split(",")[self.idx].isdigit() else self.idx
+            h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.thread = None
+            return False
+
+        def loop():
+            while not self.stop_flag:
+                try:
+                    self.samples.append((time.perf_counter(), float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)),
+                                         int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))))
+                except Exception:
+                    pass
+                time.sleep(0.2)
+        self.thread = threading.Thread(target=loop, daemon=True)
+        self.thread.start()
+        return True
+
+    def stop(self):
+        if self.thread is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"]}
+        self.stop_flag = True
+        self.thread.join()
+        sel = [x for x in self.samples if x[0] >= self.t_mark] or self.samples      # the timed region's samples
+        clk = sorted(x[1] for x in sel)
+        mask = 0
+        for x in sel:
+            mask |= x[2]
+        busy = clk[len(clk) // 2:] if clk else []
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": self.mx,
+                "reasons": sorted(n for b, n in self.REASONS.items() if mask & b), "samples": len(sel),
+                "source": "NVML in-process, 200 ms, samples taken during the timed region"}
+
+    def mark(self):
+        """Call right before the timed region: only later samples are reported."""
+        self.t_mark = time.perf_counter()
+
+
+def make_clock_sampler(gpu_index):
+    """NVML in-process by default, `nvidia-smi -lms` with UCN_CLOCKS=smi, nothing with UCN_CLOCKS=off (diagnostics only)."""
+    mode = os.environ.get("UCN_CLOCKS", "nvml")
+    if mode == "off":
+        return None
+    if mode == "nvml":
+        s = NvmlClockSampler(gpu_index)
+        if s.start():
+            s.start = lambda: None                       # already running
+            return s
+    return ClockSampler(gpu_index)
 
 
 def cpu_sample_rays(O, osc, ow, H, W, S, target_s, row0):
@@ -232,7 +308,11 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
             if d is not None:
                 torch.cuda.current_stream().wait_event(d)
 
+    host_delay = float(os.environ.get("UCN_BENCH_HOST_DELAY_MS", "0")) * 1e-3   # diagnostic: does host time add to the frame?
+
     def step_resident(timers, seed, i=0):
+        if host_delay:
+            time.sleep(host_delay)
         if side is not None and done[i & 1] is not None:
             torch.cuda.current_stream().wait_event(done[i & 1])      # buffer i&1: frame i-2 is complete (and consumed)
         fr = pack(resident)
@@ -302,10 +382,10 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
     # nvidia-smi is started BEFORE the warm-up: its start-up (NVML initialisation, first driver queries) has been seen to
     # stall kernel launches for ~0.4 s, which is most of a 5-step timed region (two runs at 124-130 ms per frame); its
     # samples then cover warm-up + timed region, both under load
-    sampler = ClockSampler(local) if full else None
-    if rank == 0 and sampler:
+    sampler = make_clock_sampler(local) if (full and rank == 0) else None
+    if sampler:
         sampler.start()
-        time.sleep(0.5)
+        time.sleep(0.3)
     for i in range(warmup):
         step_resident(None, 1000 + i, i)
     do_e2e = peer_mode or not split
@@ -317,6 +397,8 @@ def measure_render(args, wl_key, steps, warmup, ctx, full=True, replicas=False):
     # cost the frame 3-4 % (no back-to-back launches), which is why they are kept out of `value`.
     bar_ev.clear()
     L.launch_count(reset=True)
+    if sampler:
+        sampler.mark()
     ms, wall_ms = timed(lambda i: step_resident(None, i, i), steps)
     submit_ms = host_submit.get("ms")
     launches = L.launch_count() // steps

@@ -203,15 +203,18 @@ def measure(args, ClockSampler, peaks, ctx, full=True):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms[0].item() / steps, ms[1].item() / steps
 
-    sampler = ClockSampler(local) if full else None      # started before the warm-up: see bench.measure_render
-    if rank == 0 and sampler:
+    import bench as _bench
+    sampler = _bench.make_clock_sampler(local) if (full and rank == 0) else None   # before the warm-up: see bench.measure_render
+    if sampler:
         sampler.start()
-        time.sleep(0.5)
+        time.sleep(0.3)
     for i in range(max(3, args.warmup)):
         step(i, read_loss=True)
     loss0 = box["loss"]
     timers = []
     L.launch_count(reset=True)
+    if sampler:
+        sampler.mark()
     ms, wall_ms = timed(lambda i: step(100 + i, timers), args.steps)
     launches = L.launch_count() // args.steps
     clocks = sampler.stop() if (rank == 0 and sampler) else None
