@@ -113,7 +113,7 @@ class ClockSampler:
 
 
 class NvmlClockSampler:
-    """The same quantities through NVML in this process (a thread polling every 200 ms): SM clock, max SM clock and the
+    """The same quantities through NVML in this process (a thread polling every 50 ms): SM clock, max SM clock and the
     throttle-reason bit mask.  `nvidia-smi -lms` polling the recipe's nine fields (power.draw among them) during the timed
     region was measured to slow the timed region itself down -- 37.7 -> 49.2 ms per frame with host submission going from
     0.6 to 12 ms per frame -- so it is the fallback (UCN_CLOCKS=smi), not the default."""
@@ -142,7 +142,7 @@ class NvmlClockSampler:
                                          int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))))
                 except Exception:
                     pass
-                time.sleep(0.2)
+                time.sleep(0.05)
         self.thread = threading.Thread(target=loop, daemon=True)
         self.thread.start()
         return True
@@ -160,7 +160,7 @@ class NvmlClockSampler:
         busy = clk[len(clk) // 2:] if clk else []
         return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": self.mx,
                 "reasons": sorted(n for b, n in self.REASONS.items() if mask & b), "samples": len(sel),
-                "source": "NVML in-process, 200 ms, samples taken during the timed region"}
+                "source": "NVML in-process, 50 ms, samples taken during the timed region"}
 
     def mark(self):
         """Call right before the timed region: only later samples are reported."""
